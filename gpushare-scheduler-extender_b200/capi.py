@@ -1,0 +1,274 @@
+"""ctypes binding of include/gpushare_b200.h.
+
+This is plumbing for tests, bench.py and the multi-GPU driver; the product is the C-ABI library.
+There is no CPU fallback: a missing library or a missing GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+GS_OK, GS_ERR_INVALID, GS_ERR_CUDA, GS_ERR_CAPACITY, GS_ERR_NOMEM = 0, -1, -2, -3, -4
+NODE_OK, NODE_NOT_FOUND, NODE_NOT_SHARE = 0, 1, 2
+EV_ADD, EV_REMOVE = 0, 1
+POD_VALID, POD_COUNTED = 1, 2
+BIND_NO_DEVICE, BIND_NODE_NOT_FOUND = -1, -2
+MAX_DEVS, MAX_BATCH = 64, 16384
+K_REBUILD, K_APPLY, K_SORT, K_NODE_RANK, K_EXPAND, K_BIND_SORT, K_BIND_SCAN = range(7)
+KERNEL_NAMES = ["rebuild", "apply", "sort", "node_rank", "expand", "bind_sort", "bind_scan"]
+
+# numpy mirrors of the C structs (layouts asserted against sizeof in tests/test_abi.py)
+NODE_DT = np.dtype([("dev_capacity", "<u8"), ("node_idx", "<u4"), ("dev_count", "<u4"),
+                    ("node_class", "u1"), ("pad_", "u1", (7,))])
+POD_DT = np.dtype([("mem", "<u8"), ("node_idx", "<u4"), ("dev", "<i2"), ("flags", "u1"), ("pad_", "u1")])
+EVENT_DT = np.dtype([("mem", "<u8"), ("slot", "<u4"), ("node_idx", "<u4"), ("dev", "<i2"), ("op", "u1"),
+                     ("counted", "u1"), ("pad_", "<u4")])
+BIND_DT = np.dtype([("req", "<u8"), ("commit_mem", "<u8"), ("node_idx", "<u4"), ("slot", "<u4"),
+                    ("counted", "u1"), ("pad_", "u1", (7,))])
+assert NODE_DT.itemsize == 24 and POD_DT.itemsize == 16 and EVENT_DT.itemsize == 24 and BIND_DT.itemsize == 32
+
+EXPORTS = [
+    "gs_last_error", "gs_abi_version", "gs_device_count", "gs_snapshot_create", "gs_snapshot_destroy",
+    "gs_node_upsert", "gs_node_count", "gs_pods_load", "gs_rebuild", "gs_pods_apply", "gs_filter_batch",
+    "gs_filter_batch_device", "gs_node_classes", "gs_bind_batch", "gs_bind_rollback", "gs_inspect",
+    "gs_read_used", "gs_read_pods", "gs_host_alloc", "gs_host_free", "gs_profile_enable", "gs_profile_read",
+    "gs_profile_reset", "gs_launch_count", "gs_device_ptrs",
+]
+
+
+class GpushareError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"gpushare_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def library_path() -> str:
+    return _build.LIB
+
+
+def load():
+    """dlopen the in-tree library (building it first if sources are newer). Raises if it cannot."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    if _build.stale():
+        path = _build.build_native()
+    if not os.path.exists(path):
+        raise GpushareError(GS_ERR_CUDA, f"{path} is missing and could not be built; there is no CPU fallback")
+    L = C.CDLL(path)
+    vp, u32, u64p = C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64)
+    sig = {
+        "gs_last_error": (C.c_char_p, []),
+        "gs_abi_version": (C.c_int, []),
+        "gs_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+        "gs_snapshot_create": (C.c_int, [C.c_int, u32, u32, u32, C.POINTER(vp)]),
+        "gs_snapshot_destroy": (C.c_int, [vp]),
+        "gs_node_upsert": (C.c_int, [vp, vp, u32]),
+        "gs_node_count": (C.c_int, [vp, C.POINTER(u32)]),
+        "gs_pods_load": (C.c_int, [vp, vp, u32, u32]),
+        "gs_rebuild": (C.c_int, [vp]),
+        "gs_pods_apply": (C.c_int, [vp, vp, u32]),
+        "gs_filter_batch": (C.c_int, [vp, vp, u32, vp, u32]),
+        "gs_filter_batch_device": (C.c_int, [vp, vp, u32, vp, u32, vp]),
+        "gs_node_classes": (C.c_int, [vp, vp, u32]),
+        "gs_bind_batch": (C.c_int, [vp, vp, u32, vp]),
+        "gs_bind_rollback": (C.c_int, [vp, vp, u32]),
+        "gs_inspect": (C.c_int, [vp, u32, vp, vp, u32, C.POINTER(u32), C.POINTER(C.c_uint8)]),
+        "gs_read_used": (C.c_int, [vp, u32, u32, vp]),
+        "gs_read_pods": (C.c_int, [vp, u32, u32, vp]),
+        "gs_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(vp)]),
+        "gs_host_free": (C.c_int, [vp]),
+        "gs_profile_enable": (C.c_int, [vp, C.c_int]),
+        "gs_profile_read": (C.c_int, [vp, C.c_int, u64p, C.POINTER(C.c_double)]),
+        "gs_profile_reset": (C.c_int, [vp]),
+        "gs_launch_count": (C.c_int, [vp, u64p]),
+        "gs_device_ptrs": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != GS_OK:
+        raise GpushareError(rc, load().gs_last_error().decode(errors="replace"))
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class PinnedBuffer:
+    """Page-locked host memory from gs_host_alloc, viewed as a numpy array."""
+
+    def __init__(self, shape, dtype):
+        self.shape = tuple(shape) if not np.isscalar(shape) else (int(shape),)
+        self.dtype = np.dtype(dtype)
+        nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        p = C.c_void_p()
+        _check(load().gs_host_alloc(max(nbytes, 1), C.byref(p)))
+        self.ptr = p.value
+        self.nbytes = nbytes
+        buf = (C.c_char * max(nbytes, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            load().gs_host_free(C.c_void_p(self.ptr))
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Snapshot:
+    """One GPU's struct-of-arrays cluster snapshot (the stand-in for cache.SchedulerCache state)."""
+
+    def __init__(self, max_nodes: int, max_devs: int = 8, max_pods: int = 1, device: int = 0):
+        L = load()
+        h = C.c_void_p()
+        _check(L.gs_snapshot_create(device, max_nodes, max_devs, max_pods, C.byref(h)))
+        self.h = h
+        self.max_nodes, self.max_devs, self.max_pods, self.device = max_nodes, max_devs, max_pods, device
+
+    def close(self):
+        if getattr(self, "h", None):
+            load().gs_snapshot_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- nodes ----
+    def node_upsert(self, nodes: np.ndarray):
+        nodes = np.ascontiguousarray(nodes, dtype=NODE_DT)
+        _check(load().gs_node_upsert(self.h, _ptr(nodes), len(nodes)))
+
+    def upsert_nodes(self, node_idx, dev_capacity, dev_count, node_class):
+        n = len(node_idx)
+        a = np.zeros(n, dtype=NODE_DT)
+        a["node_idx"], a["dev_capacity"], a["dev_count"], a["node_class"] = node_idx, dev_capacity, dev_count, node_class
+        self.node_upsert(a)
+
+    @property
+    def node_count(self) -> int:
+        v = C.c_uint32()
+        _check(load().gs_node_count(self.h, C.byref(v)))
+        return v.value
+
+    @property
+    def bitmap_words(self) -> int:
+        return (self.node_count + 31) // 32
+
+    def node_classes(self, n=None) -> np.ndarray:
+        n = self.node_count if n is None else n
+        out = np.empty(n, dtype=np.uint8)
+        _check(load().gs_node_classes(self.h, _ptr(out), n))
+        return out
+
+    # ---- pods ----
+    def pods_load(self, recs: np.ndarray, first_slot: int = 0):
+        recs = np.ascontiguousarray(recs, dtype=POD_DT)
+        _check(load().gs_pods_load(self.h, _ptr(recs), first_slot, len(recs)))
+
+    def rebuild(self):
+        _check(load().gs_rebuild(self.h))
+
+    def pods_apply(self, events: np.ndarray):
+        events = np.ascontiguousarray(events, dtype=EVENT_DT)
+        _check(load().gs_pods_apply(self.h, _ptr(events), len(events)))
+
+    # ---- filter ----
+    def filter_batch(self, req, row_stride_words: int | None = None, out: np.ndarray | None = None) -> np.ndarray:
+        req = np.ascontiguousarray(req, dtype=np.uint64)
+        stride = row_stride_words if row_stride_words is not None else (self.bitmap_words + 3) // 4 * 4
+        if out is None:
+            out = np.empty((len(req), stride), dtype=np.uint32)
+        assert out.dtype == np.uint32 and out.flags.c_contiguous and out.shape == (len(req), stride)
+        _check(load().gs_filter_batch(self.h, _ptr(req), len(req), _ptr(out), stride))
+        return out
+
+    def filter_batch_device(self, d_req_ptr: int, n_pods: int, d_out_ptr: int, row_stride_words: int, stream: int = 0):
+        _check(load().gs_filter_batch_device(self.h, C.c_void_p(d_req_ptr), n_pods, C.c_void_p(d_out_ptr),
+                                             row_stride_words, C.c_void_p(stream)))
+
+    # ---- bind ----
+    def bind_batch(self, binds: np.ndarray) -> np.ndarray:
+        binds = np.ascontiguousarray(binds, dtype=BIND_DT)
+        out = np.empty(len(binds), dtype=np.int32)
+        _check(load().gs_bind_batch(self.h, _ptr(binds), len(binds), _ptr(out)))
+        return out
+
+    def bind_rollback(self, slots):
+        slots = np.ascontiguousarray(slots, dtype=np.uint32)
+        _check(load().gs_bind_rollback(self.h, _ptr(slots), len(slots)))
+
+    # ---- read-back ----
+    def inspect(self, node_idx: int):
+        cap = np.zeros(self.max_devs, dtype=np.uint64)
+        used = np.zeros(self.max_devs, dtype=np.uint64)
+        nd, cls = C.c_uint32(), C.c_uint8()
+        _check(load().gs_inspect(self.h, node_idx, _ptr(cap), _ptr(used), self.max_devs, C.byref(nd), C.byref(cls)))
+        return cap[: nd.value].copy(), used[: nd.value].copy(), cls.value
+
+    def read_used(self, first_node: int = 0, n: int | None = None) -> np.ndarray:
+        n = self.node_count - first_node if n is None else n
+        out = np.empty((n, self.max_devs), dtype=np.uint64)
+        _check(load().gs_read_used(self.h, first_node, n, _ptr(out)))
+        return out
+
+    def read_pods(self, first_slot: int, n: int) -> np.ndarray:
+        out = np.empty(n, dtype=POD_DT)
+        _check(load().gs_read_pods(self.h, first_slot, n, _ptr(out)))
+        return out
+
+    # ---- profiling ----
+    def profile(self, on: bool):
+        _check(load().gs_profile_enable(self.h, 1 if on else 0))
+
+    def profile_reset(self):
+        _check(load().gs_profile_reset(self.h))
+
+    def profile_read(self) -> dict:
+        res = {}
+        for kid, name in enumerate(KERNEL_NAMES):
+            n, ms = C.c_uint64(), C.c_double()
+            _check(load().gs_profile_read(self.h, kid, C.byref(n), C.byref(ms)))
+            res[name] = (n.value, ms.value)
+        return res
+
+    @property
+    def launch_count(self) -> int:
+        v = C.c_uint64()
+        _check(load().gs_launch_count(self.h, C.byref(v)))
+        return v.value
+
+
+def unpack_bitmap(bitmap: np.ndarray, n_nodes: int) -> np.ndarray:
+    """[P][stride] uint32 words -> [P][n_nodes] bool (bit n&31 of word n>>5)."""
+    b = np.unpackbits(np.ascontiguousarray(bitmap).view(np.uint8), axis=1, bitorder="little")
+    return b[:, :n_nodes].astype(bool)

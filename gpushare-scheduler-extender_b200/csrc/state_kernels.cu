@@ -1,0 +1,254 @@
+// K1 (cache rebuild), K2 (incremental pod events) and K4 (ordered per-node binpack).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gs {
+
+using u64 = unsigned long long;
+
+__device__ __forceinline__ gs_pod_record load_record(const gs_pod_record* p) {
+    static_assert(sizeof(gs_pod_record) == 16, "record is one 128-bit load");
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    gs_pod_record r;
+    *reinterpret_cast<uint4*>(&r) = v;
+    return r;
+}
+__device__ __forceinline__ void store_record(gs_pod_record* p, const gs_pod_record& r) {
+    *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(&r);
+}
+
+// a record may only name a device the node really has: nodeinfo.go:98-108 (`dev, found := n.devs[id]`)
+__device__ __forceinline__ bool legal_device(const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, uint32_t node,
+                                             int dev) {
+    if (node >= n_nodes || dev < 0) return false;
+    return (uint32_t)dev < nodeinfo_ndev(nodeinfo[node]);
+}
+
+__global__ void k_fill_i32(int32_t* d, int32_t v, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) d[i] = v;
+}
+
+__global__ void k_validate_records(gs_pod_record* pods, uint32_t first, uint32_t n, const uint32_t* __restrict__ nodeinfo,
+                                   uint32_t n_nodes) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    gs_pod_record r = load_record(pods + first + i);
+    if ((r.flags & GS_POD_VALID) && !legal_device(nodeinfo, n_nodes, r.node_idx, r.dev)) {
+        r.flags = 0;
+        store_record(pods + first + i, r);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: used[node][dev] = sum of mem over valid, counted records (pkg/cache/deviceinfo.go:41-54 as a
+// segmented integer reduction).  Each warp reduces runs of equal (node, dev) with shuffles, so a pod
+// table grouped by node issues one atomic per run; run totals go to a shared-memory window of bins
+// anchored at the CTA's first record and only what falls outside it goes straight to global atomics.
+// ------------------------------------------------------------------------------------------------
+constexpr int kRebuildThreads = 256;
+constexpr int kRebuildItems = 8;           // records per thread
+constexpr uint32_t kRebuildWindow = 2048;  // bins privatised per CTA (16 KB)
+
+__global__ void __launch_bounds__(kRebuildThreads)
+k_rebuild(const gs_pod_record* __restrict__ pods, uint32_t n_slots, uint32_t dev_stride, u64* __restrict__ used) {
+    __shared__ u64 win[kRebuildWindow];
+    __shared__ uint32_t win_base;
+    const uint32_t tid = threadIdx.x, lane = tid & 31;
+    const uint32_t cta_first = blockIdx.x * (kRebuildThreads * kRebuildItems);
+    for (uint32_t i = tid; i < kRebuildWindow; i += kRebuildThreads) win[i] = 0;
+    if (tid == 0) {
+        gs_pod_record r0 = load_record(pods + cta_first);
+        win_base = r0.node_idx * dev_stride;  // any anchor is correct; this one suits node-grouped tables
+    }
+    __syncthreads();
+    const uint32_t base = win_base;
+
+#pragma unroll
+    for (int it = 0; it < kRebuildItems; ++it) {
+        const uint32_t i = cta_first + it * kRebuildThreads + tid;
+        uint32_t bin = 0xffffffffu;
+        u64 val = 0;
+        if (i < n_slots) {
+            gs_pod_record r = load_record(pods + i);
+            if ((r.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED)) {
+                bin = r.node_idx * dev_stride + (uint32_t)r.dev;
+                val = r.mem;
+            }
+        }
+        // segmented inclusive scan over runs of equal bins
+        const uint32_t prev = __shfl_up_sync(0xffffffffu, bin, 1);
+        const bool head = (lane == 0) || (prev != bin);
+        const uint32_t heads = __ballot_sync(0xffffffffu, head);
+        const uint32_t seg_start = 31u - __clz(heads & (0xffffffffu >> (31 - lane)));
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            u64 t = __shfl_up_sync(0xffffffffu, val, o);
+            if (lane >= seg_start + o) val += t;
+        }
+        const bool tail = (lane == 31) || ((heads >> (lane + 1)) & 1u);
+        if (tail && bin != 0xffffffffu && val != 0) {
+            const uint32_t rel = bin - base;
+            if (rel < kRebuildWindow)
+                atomicAdd(&win[rel], val);
+            else
+                atomicAdd(&used[bin], val);
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < kRebuildWindow; i += kRebuildThreads) {
+        u64 v = win[i];
+        if (v) atomicAdd(&used[base + i], v);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: pod events (pkg/cache/cache.go:89-127, deviceinfo.go:56-80).  A slot's final state is that of
+// its last effective event in the batch and additions commute mod 2^64, so: pass 1 finds the last
+// effective event per slot, pass 2 applies exactly those.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool event_effective(const gs_pod_event& e, uint32_t max_pods,
+                                                const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes) {
+    if (e.slot >= max_pods) return false;
+    if (e.op == GS_EV_REMOVE) return true;
+    return legal_device(nodeinfo, n_nodes, e.node_idx, e.dev);
+}
+
+__global__ void k_events_mark(const gs_pod_event* __restrict__ ev, uint32_t n, uint32_t max_pods, int32_t* last_ev,
+                              const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    gs_pod_event e = ev[i];
+    if (event_effective(e, max_pods, nodeinfo, n_nodes)) atomicMax(&last_ev[e.slot], (int32_t)i);
+}
+
+__global__ void k_events_apply(const gs_pod_event* __restrict__ ev, uint32_t n, gs_pod_record* pods, uint32_t max_pods,
+                               int32_t* last_ev, const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes,
+                               uint32_t dev_stride, u64* used) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    gs_pod_event e = ev[i];
+    if (!event_effective(e, max_pods, nodeinfo, n_nodes)) return;
+    if (last_ev[e.slot] != (int32_t)i) return;
+    last_ev[e.slot] = -1;  // leave the scratch table idle for the next batch
+    gs_pod_record old = load_record(pods + e.slot);
+    if ((old.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED) && old.mem)
+        atomicAdd(&used[(size_t)old.node_idx * dev_stride + (uint32_t)old.dev], 0ull - old.mem);
+    gs_pod_record now;
+    now.mem = 0;
+    now.node_idx = 0;
+    now.dev = 0;
+    now.flags = 0;
+    now.pad_ = 0;
+    if (e.op == GS_EV_ADD) {
+        now.mem = e.mem;
+        now.node_idx = e.node_idx;
+        now.dev = e.dev;
+        now.flags = (uint8_t)(GS_POD_VALID | (e.counted ? GS_POD_COUNTED : 0u));
+        if (e.counted && e.mem) atomicAdd(&used[(size_t)e.node_idx * dev_stride + (uint32_t)e.dev], e.mem);
+    }
+    store_record(pods + e.slot, now);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4: binds sorted by node (stable, so queue order survives inside a node); the thread that sees the
+// first bind of a node walks that node's binds in order: allocateGPUID (nodeinfo.go:209-252) then the
+// commit of Allocate (nodeinfo.go:190-203).
+// ------------------------------------------------------------------------------------------------
+__global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, const u64* __restrict__ sorted_nodes,
+                            const uint16_t* __restrict__ perm, gs_pod_record* pods, uint32_t max_pods,
+                            const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, const u64* __restrict__ cap,
+                            uint32_t dev_stride, u64* used, int32_t* __restrict__ out_dev) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const u64 node64 = sorted_nodes[j];
+    if (j > 0 && sorted_nodes[j - 1] == node64) return;  // not the head of its node's run
+    const uint32_t node = (uint32_t)node64;
+    const bool known = node < n_nodes && nodeinfo_class(nodeinfo[node]) != GS_NODE_NOT_FOUND;
+    const uint32_t ndev = known ? nodeinfo_ndev(nodeinfo[node]) : 0u;
+    const u64 c = known ? cap[node] : 0ull;
+    u64* row = used + (size_t)node * dev_stride;
+    for (uint32_t k = j; k < n && sorted_nodes[k] == node64; ++k) {
+        const uint32_t bi = perm[k];
+        const gs_bind_req b = binds[bi];
+        if (!known) {
+            out_dev[bi] = GS_BIND_NODE_NOT_FOUND;
+            continue;
+        }
+        int cand = -1;
+        u64 cand_mem = 0;
+        if (b.req > 0) {
+            for (uint32_t d = 0; d < ndev; ++d) {
+                const u64 avail = c - row[d];
+                if (avail >= b.req) {
+                    if (cand == -1 || cand_mem > avail) {
+                        cand = (int)d;
+                        cand_mem = avail;
+                    }
+                }
+            }
+        }
+        out_dev[bi] = cand;
+        if (cand >= 0 && b.slot < max_pods) {
+            gs_pod_record old = load_record(pods + b.slot);
+            if ((old.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED) && old.mem) {
+                if (old.node_idx == node)
+                    row[old.dev] -= old.mem;  // same UID re-added on this node: replace, do not double count
+                else
+                    atomicAdd(&used[(size_t)old.node_idx * dev_stride + (uint32_t)old.dev], 0ull - old.mem);
+            }
+            gs_pod_record now;
+            now.mem = b.commit_mem;
+            now.node_idx = node;
+            now.dev = (int16_t)cand;
+            now.flags = (uint8_t)(GS_POD_VALID | (b.counted ? GS_POD_COUNTED : 0u));
+            now.pad_ = 0;
+            store_record(pods + b.slot, now);
+            if (b.counted) row[cand] += b.commit_mem;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+cudaError_t launch_fill_i32(int32_t* d, int32_t v, size_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_fill_i32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d, v, n);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_validate_records(gs_pod_record* d_pods, uint32_t first, uint32_t n, const uint32_t* d_nodeinfo,
+                                    uint32_t n_nodes, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_validate_records<<<(n + 255) / 256, 256, 0, st>>>(d_pods, first, n, d_nodeinfo, n_nodes);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rebuild(const gs_pod_record* d_pods, uint32_t n_slots, uint32_t dev_stride, u64* d_used,
+                           int /*sm_count*/, cudaStream_t st) {
+    if (n_slots == 0) return cudaSuccess;
+    const uint32_t per_cta = kRebuildThreads * kRebuildItems;
+    k_rebuild<<<(n_slots + per_cta - 1) / per_cta, kRebuildThreads, 0, st>>>(d_pods, n_slots, dev_stride, d_used);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_apply_events(const gs_pod_event* d_events, uint32_t n, gs_pod_record* d_pods, uint32_t max_pods,
+                                int32_t* d_last_ev, const uint32_t* d_nodeinfo, uint32_t n_nodes,
+                                uint32_t dev_stride, u64* d_used, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const uint32_t blocks = (n + 255) / 256;
+    k_events_mark<<<blocks, 256, 0, st>>>(d_events, n, max_pods, d_last_ev, d_nodeinfo, n_nodes);
+    k_events_apply<<<blocks, 256, 0, st>>>(d_events, n, d_pods, max_pods, d_last_ev, d_nodeinfo, n_nodes, dev_stride,
+                                           d_used);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bind_scan(const gs_bind_req* d_binds, uint32_t n, const u64* d_sorted_nodes, const uint16_t* d_perm,
+                             gs_pod_record* d_pods, uint32_t max_pods, const uint32_t* d_nodeinfo, uint32_t n_nodes,
+                             const u64* d_cap, uint32_t dev_stride, u64* d_used, int32_t* d_out_dev, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_bind_scan<<<(n + 127) / 128, 128, 0, st>>>(d_binds, n, d_sorted_nodes, d_perm, d_pods, max_pods, d_nodeinfo,
+                                                 n_nodes, d_cap, dev_stride, d_used, d_out_dev);
+    return cudaGetLastError();
+}
+
+}  // namespace gs

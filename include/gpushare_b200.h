@@ -1,0 +1,205 @@
+/*
+ * gpushare_b200.h -- C ABI of the B200-native gpushare scheduling hot path.
+ *
+ * This is the seam a maintainer of bnulwh/gpushare-scheduler-extender binds with cgo in place of the
+ * in-memory `*cache.SchedulerCache` (pkg/cache/cache.go:14-28): the cluster lives on the GPU as a
+ * struct-of-arrays snapshot, and the three hot loops of the reference run as CUDA kernels:
+ *
+ *   reference                                                     | entry point here
+ *   --------------------------------------------------------------+----------------------------
+ *   NewNodeInfo                  pkg/cache/nodeinfo.go:29-45       | gs_node_upsert
+ *   BuildCache + DeviceInfo.GetUsedGPUMemory                       | gs_pods_load + gs_rebuild (K1)
+ *                                pkg/cache/cache.go:49-74,         |
+ *                                pkg/cache/deviceinfo.go:41-54     |
+ *   AddOrUpdatePod / RemovePod   pkg/cache/cache.go:89-127,        | gs_pods_apply (K2)
+ *     addPod / removePod         pkg/cache/deviceinfo.go:56-80     |
+ *   Predicate.Handler loop over NodeInfo.Assume                    | gs_filter_batch (K3)
+ *                                pkg/scheduler/predicate.go:15-39, |
+ *                                pkg/cache/nodeinfo.go:113-137     |
+ *   NodeInfo.allocateGPUID + the commit in Allocate                | gs_bind_batch (K4),
+ *                                pkg/cache/nodeinfo.go:139-252     | gs_bind_rollback
+ *   Inspect buildNode            pkg/scheduler/inspect.go:33-71    | gs_inspect
+ *
+ * Strings never cross this boundary: the host side keeps name->node_idx and (UID,node,dev)->slot
+ * tables, parses annotations once at ingestion and renders the reference's reason strings.
+ * Every integer is the reference's 64-bit Go int/uint; `uint` wrap-around is reproduced.
+ *
+ * Conventions: every function returns GS_OK (0) or a negative GS_ERR_* code and never throws or
+ * aborts; gs_last_error() gives the message for the calling thread.  Host buffers belong to the
+ * caller and are only touched during the call (cgo's pointer rule).  Calls on one snapshot are
+ * serialised by an internal lock; different snapshots (one per GPU) are independent.  Each call
+ * makes the snapshot's device current for the calling thread.
+ *
+ * There is no CPU fallback: without a CUDA device gs_snapshot_create fails with GS_ERR_CUDA.
+ */
+#ifndef GPUSHARE_B200_H
+#define GPUSHARE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS_ABI_VERSION 1
+
+enum {
+    GS_OK = 0,
+    GS_ERR_INVALID = -1,  /* bad argument                                   */
+    GS_ERR_CUDA = -2,     /* CUDA runtime error (message in gs_last_error)  */
+    GS_ERR_CAPACITY = -3, /* index beyond what the snapshot was created for */
+    GS_ERR_NOMEM = -4
+};
+
+/* Outcome classes of GetNodeInfo + IsGPUSharingNode (pkg/scheduler/gpushare-predicate.go:18-25). */
+enum {
+    GS_NODE_OK = 0,        /* in the node lister and gpu-mem capacity > 0                          */
+    GS_NODE_NOT_FOUND = 1, /* `node "<name>" not found`                                            */
+    GS_NODE_NOT_SHARE = 2  /* `The node <name> is not for GPU share, need skip`                    */
+};
+
+/* Most devices a node may have (len(NodeInfo.devs), pkg/cache/nodeinfo.go:32-35). */
+#define GS_MAX_DEVS 64
+/* Rows one filter / bind launch handles; larger batches are split internally. */
+#define GS_MAX_BATCH 16384
+
+/* One node as NewNodeInfo freezes it (pkg/cache/nodeinfo.go:29-45). */
+typedef struct gs_node {
+    uint64_t dev_capacity; /* uint(total / count), identical for every device of the node */
+    uint32_t node_idx;
+    uint32_t dev_count; /* gpu-count (<= 0 in the reference -> 0 here)                          */
+    uint8_t node_class; /* GS_NODE_*                                                            */
+    uint8_t pad_[7];
+} gs_node;
+
+#define GS_POD_VALID 1u   /* the slot holds an entry of some DeviceInfo.podMap                      */
+#define GS_POD_COUNTED 2u /* phase is neither Succeeded nor Failed (pkg/cache/deviceinfo.go:46-49)  */
+
+/* One podMap entry: pod -> (node, gpu-id, mem).  `mem` is GetGPUMemoryFromPodAnnotation
+ * (pkg/utils/pod.go:94-113), `dev` GetGPUIDFromAnnotation (pod.go:45-60) clamped to int16. */
+typedef struct gs_pod_record {
+    uint64_t mem;
+    uint32_t node_idx;
+    int16_t dev;
+    uint8_t flags; /* GS_POD_* */
+    uint8_t pad_;
+} gs_pod_record;
+
+enum { GS_EV_ADD = 0, GS_EV_REMOVE = 1 };
+
+/* One cache mutation.  ADD on a live slot replaces it (deviceinfo.go:63: same UID, same device);
+ * REMOVE of a dead slot is a no-op.  Events of one batch apply in array order. */
+typedef struct gs_pod_event {
+    uint64_t mem;
+    uint32_t slot;
+    uint32_t node_idx;
+    int16_t dev;
+    uint8_t op;      /* GS_EV_* */
+    uint8_t counted; /* 0/1, see GS_POD_COUNTED */
+    uint32_t pad_;
+} gs_pod_event;
+
+/* One Bind.  `req` is uint(GetGPUMemoryFromPodResource) (nodeinfo.go:217); `commit_mem` is what the
+ * committed pod's annotation will read back as (max(0, int(req)), pod.go:98-101); `slot` is a free
+ * slot that receives the new podMap entry when a device is found. */
+typedef struct gs_bind_req {
+    uint64_t req;
+    uint64_t commit_mem;
+    uint32_t node_idx;
+    uint32_t slot;
+    uint8_t counted;
+    uint8_t pad_[7];
+} gs_bind_req;
+
+#define GS_BIND_NO_DEVICE (-1)      /* allocateGPUID found nothing: "can't place the pod"        */
+#define GS_BIND_NODE_NOT_FOUND (-2) /* GetNodeInfo failed for node_idx                           */
+
+typedef struct gs_snapshot gs_snapshot;
+
+/* Per-kernel device-time counters (CUDA events on the launching stream), for bench.py. */
+enum {
+    GS_K_REBUILD = 0,
+    GS_K_APPLY = 1,
+    GS_K_SORT = 2,
+    GS_K_NODE_RANK = 3,
+    GS_K_EXPAND = 4,
+    GS_K_BIND_SORT = 5,
+    GS_K_BIND_SCAN = 6,
+    GS_K_COUNT_ = 7
+};
+
+const char* gs_last_error(void);
+int gs_abi_version(void);
+int gs_device_count(int* out_count);
+
+/* Replaces NewSchedulerCache (pkg/cache/cache.go:30-38).  max_devs is the row stride of the
+ * node x device arrays (1..GS_MAX_DEVS). */
+int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32_t max_pods,
+                       gs_snapshot** out);
+int gs_snapshot_destroy(gs_snapshot* s);
+
+/* Replaces NewNodeInfo / the replacement branch of GetNodeInfo (cache.go:139-157).  Upserting a
+ * node does NOT touch its used[] row; the caller removes the node's pods when the reference would
+ * drop the podMaps. */
+int gs_node_upsert(gs_snapshot* s, const gs_node* nodes, uint32_t n);
+/* Nodes covered by filter bitmaps: 1 + the largest node_idx ever upserted. */
+int gs_node_count(gs_snapshot* s, uint32_t* out_nodes);
+
+/* Replaces the pod loop of BuildCache (cache.go:56-69): writes records into slots
+ * [first_slot, first_slot + n).  Records whose (node, dev) is not a device of the snapshot are
+ * stored invalid, as nodeinfo.go:98-108 would not add them.  Does not change used[]; follow with
+ * gs_rebuild. */
+int gs_pods_load(gs_snapshot* s, const gs_pod_record* recs, uint32_t first_slot, uint32_t n);
+/* K1: used[node][dev] = sum of mem over valid, counted records (deviceinfo.go:41-54). */
+int gs_rebuild(gs_snapshot* s);
+/* K2: AddOrUpdatePod / RemovePod deltas (cache.go:89-127). */
+int gs_pods_apply(gs_snapshot* s, const gs_pod_event* events, uint32_t n);
+
+/* K3: the Predicate.Handler loop for a batch of pending pods against every node.
+ * req[p] = uint(GetGPUMemoryFromPodResource(pod p)).  out_bitmap is [n_pods][row_stride_words]
+ * 32-bit words, bit (n & 31) of word (n >> 5) of row p set iff the predicate passes for node n;
+ * row_stride_words >= ceil(node_count / 32); padding words up to the next multiple of 4 may be
+ * written as zero.  A zero bit on a GS_NODE_OK node means "Insufficient GPU Memory in one device".
+ * Fastest when row_stride_words is a multiple of 4 and out_bitmap came from gs_host_alloc. */
+int gs_filter_batch(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint32_t* out_bitmap,
+                    uint32_t row_stride_words);
+/* Same, with req and out_bitmap in device memory of the snapshot's GPU; asynchronous on
+ * `cuda_stream` (a cudaStream_t; NULL = the snapshot's own stream).  Calls on one snapshot must be
+ * ordered by the caller (they share the snapshot's work buffers). */
+int gs_filter_batch_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods,
+                           uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream);
+/* Per-node class bytes (GS_NODE_*) for rendering FailedNodes. */
+int gs_node_classes(gs_snapshot* s, uint8_t* out_class, uint32_t n);
+
+/* K4: allocateGPUID + commit for a queue of binds, applied in array order per node
+ * (nodeinfo.go:139-252).  out_dev[i] = chosen device, GS_BIND_NO_DEVICE or GS_BIND_NODE_NOT_FOUND.
+ * A found bind commits used[node][dev] += commit_mem (when counted) and fills `slot`. */
+int gs_bind_batch(gs_snapshot* s, const gs_bind_req* binds, uint32_t n, int32_t* out_dev);
+/* Undo commits whose apiserver Update/Bind failed (nodeinfo.go:151-168,185-188: no commit). */
+int gs_bind_rollback(gs_snapshot* s, const uint32_t* slots, uint32_t n);
+
+/* Inspect (inspect.go:33-71): per-device capacity and used memory of one node. */
+int gs_inspect(gs_snapshot* s, uint32_t node_idx, uint64_t* out_capacity, uint64_t* out_used,
+               uint32_t cap_devs, uint32_t* out_dev_count, uint8_t* out_class);
+/* Bulk read-back of used[first_node .. first_node+n)[max_devs] (row-major) and of pod records. */
+int gs_read_used(gs_snapshot* s, uint32_t first_node, uint32_t n, uint64_t* out_used);
+int gs_read_pods(gs_snapshot* s, uint32_t first_slot, uint32_t n, gs_pod_record* out);
+
+/* Pinned host memory for bitmaps / requests (lets copies run at full PCIe rate). */
+int gs_host_alloc(size_t bytes, void** out);
+int gs_host_free(void* p);
+
+/* Device-time profiling of the library's own kernels (off by default). */
+int gs_profile_enable(gs_snapshot* s, int on);
+int gs_profile_read(gs_snapshot* s, int kernel_id, uint64_t* out_launches, double* out_total_ms);
+int gs_profile_reset(gs_snapshot* s);
+/* Total kernels this snapshot has launched since creation (always counted). */
+int gs_launch_count(gs_snapshot* s, uint64_t* out_launches);
+/* Device pointers of the snapshot arrays, for zero-copy use from the same process (tests, NCCL). */
+int gs_device_ptrs(gs_snapshot* s, void** d_used, void** d_capacity, void** d_nodeinfo, void** d_pods);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

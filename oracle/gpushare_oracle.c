@@ -1229,3 +1229,36 @@ int orc_ctrl_drain(orc_cluster* c, char* err, size_t errcap) {
     }
     return rc;
 }
+
+/* ------------------------------------------------------------------------------------------ */
+/* bulk construction (test / baseline plumbing, no reference counterpart)                       */
+/* ------------------------------------------------------------------------------------------ */
+size_t orc_bulk_load(orc_cluster* c, size_t n_nodes, const int64_t* node_total, const int64_t* node_count,
+                     const uint8_t* node_listed, size_t n_pods, const int32_t* pod_node,
+                     const int64_t* pod_gpu, const int64_t* pod_mem, const uint8_t* pod_phase) {
+    char name[64], buf[32];
+    for (size_t i = 0; i < n_nodes; ++i) {
+        if (!node_listed[i]) continue;
+        snprintf(name, sizeof name, "node-%06zu", i);
+        orc_node_lister_set(c, name, node_total[i] >= 0, node_total[i] >= 0 ? node_total[i] : 0,
+                            node_count[i] >= 0, node_count[i] >= 0 ? node_count[i] : 0);
+    }
+    size_t added = 0;
+    for (size_t j = 0; j < n_pods; ++j) {
+        char pname[64], uid[64];
+        snprintf(pname, sizeof pname, "run-%zu", j);
+        snprintf(uid, sizeof uid, "uid-run-%zu", j);
+        snprintf(name, sizeof name, "node-%06zu", (size_t)pod_node[j]);
+        orc_pod* p = orc_pod_new(pname, "default", uid);
+        orc_pod_set_node_name(p, name);
+        orc_pod_set_phase(p, pod_phase[j]);
+        snprintf(buf, sizeof buf, "%lld", (long long)pod_gpu[j]);
+        orc_pod_set_annotation(p, ENV_RESOURCE_INDEX, buf);
+        snprintf(buf, sizeof buf, "%lld", (long long)pod_mem[j]);
+        orc_pod_set_annotation(p, ENV_RESOURCE_BY_POD, buf);
+        orc_pod_add_container(p, 1, pod_mem[j]);
+        if (orc_get_gpu_memory_from_pod_annotation(p) > 0 && orc_add_or_update_pod(c, p, NULL, 0) == 0) added++;
+        orc_pod_free(p);
+    }
+    return added;
+}

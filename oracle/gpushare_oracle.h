@@ -143,6 +143,14 @@ void orc_informer_delete(orc_cluster* c, const orc_pod* p);
 int orc_ctrl_drain(orc_cluster* c, char* err, size_t errcap);
 size_t orc_ctrl_queue_len(orc_cluster* c);
 
+/* Bulk construction for the timed CPU baseline: lists nodes "node-%06d" (total/count < 0 = key
+ * absent; listed[i] == 0 = not in the lister) and running pods "run-<j>" with their annotations
+ * rendered as strings, then feeds every pod through AddOrUpdatePod (pods on unlisted nodes are
+ * skipped, as syncPod would fail them).  Returns the number of pods added to the cache. */
+size_t orc_bulk_load(orc_cluster* c, size_t n_nodes, const int64_t* node_total, const int64_t* node_count,
+                     const uint8_t* node_listed, size_t n_pods, const int32_t* pod_node,
+                     const int64_t* pod_gpu, const int64_t* pod_mem, const uint8_t* pod_phase);
+
 void orc_free(void* p);
 
 #ifdef __cplusplus

@@ -95,6 +95,7 @@ def lib():
         "orc_informer_delete": (None, [vp, vp]),
         "orc_ctrl_drain": (C.c_int, [vp, cp, sz]),
         "orc_ctrl_queue_len": (sz, [vp]),
+        "orc_bulk_load": (sz, [vp, sz, vp, vp, vp, sz, vp, vp, vp, vp]),
         "orc_free": (None, [vp]),
     }
     for name, (res, args) in sig.items():
@@ -312,6 +313,17 @@ class Cluster:
             return None
         n = min(n, cap)
         return list(total[:n]), list(used[:n])
+
+    def bulk_load(self, node_total, node_count, node_listed, pod_node, pod_gpu, pod_mem, pod_phase) -> int:
+        """Fast path for big synthetic clusters (see orc_bulk_load). Phases use the oracle's enum."""
+        import numpy as np
+
+        a = [np.ascontiguousarray(node_total, np.int64), np.ascontiguousarray(node_count, np.int64),
+             np.ascontiguousarray(node_listed, np.uint8), np.ascontiguousarray(pod_node, np.int32),
+             np.ascontiguousarray(pod_gpu, np.int64), np.ascontiguousarray(pod_mem, np.int64),
+             np.ascontiguousarray(pod_phase, np.uint8)]
+        p = [x.ctypes.data_as(C.c_void_p) for x in a]
+        return lib().orc_bulk_load(self.h, len(a[0]), p[0], p[1], p[2], len(a[3]), p[3], p[4], p[5], p[6])
 
     # event path
     def informer_add(self, pod: Pod):

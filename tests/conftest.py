@@ -8,6 +8,12 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+import importlib
+
+gsx = importlib.import_module("gpushare-scheduler-extender_b200")
+sys.modules.setdefault("gsx", gsx)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
