@@ -228,7 +228,12 @@ def run_product(args):
     dev = torch.device("cuda", local_rank)
     d_req = torch.from_numpy(reqs.view(np.int64)).to(dev)
     outs = [torch.empty((P, stride), dtype=torch.int32, device=dev) for _ in range(N_OUT_BUFFERS)]
-    stream = torch.cuda.current_stream().cuda_stream
+    # a real (non-default) stream: the library treats a NULL stream as "the snapshot's own stream", and
+    # torch's events below must be recorded on the stream the kernels run on
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
 
     def step(i):
         snap.filter_batch_device(d_req.data_ptr(), P, outs[i % N_OUT_BUFFERS].data_ptr(), stride, stream)
@@ -262,16 +267,20 @@ def run_product(args):
     ms_per_step = ms_total / args.steps
     value = world * P * N / (ms_per_step * 1e-3)
 
-    # per-kernel device times, same inputs, same number of steps (library-side CUDA events on the
-    # launching stream around each of its kernels)
-    snap.profile(True)
-    snap.profile_reset()
-    for i in range(args.steps):
-        step(i)
-    torch.cuda.synchronize()
-    prof = snap.profile_read()
-    snap.profile(False)
-    kernel_ms = {k: (v[1] / v[0] if v[0] else None) for k, v in prof.items() if v[0]}
+    # per-kernel device times: CUDA events on the launching stream around `steps` back-to-back launches
+    # of ONE stage (same inputs, same rotating outputs); the stages of a step sum to ~ms_per_step
+    kernel_ms = {}
+    for name, mask in (("sort", gsx.capi.STAGE_SORT), ("node_rank", gsx.capi.STAGE_NODE_RANK), ("expand", gsx.capi.STAGE_EXPAND)):
+        for i in range(3):
+            snap.filter_stages_device(mask, d_req.data_ptr(), P, outs[i % N_OUT_BUFFERS].data_ptr(), stride, stream)
+        torch.cuda.synchronize()
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k0.record()
+        for i in range(args.steps):
+            snap.filter_stages_device(mask, d_req.data_ptr(), P, outs[i % N_OUT_BUFFERS].data_ptr(), stride, stream)
+        k1.record()
+        torch.cuda.synchronize()
+        kernel_ms[name] = k0.elapsed_time(k1) / args.steps
     t_expand = kernel_ms.get("expand")
     words_pad = (words + 127) // 128 * 128
     expand_bytes = P * words * 4 + words_pad * 64 + P * 2       # bitmap written + rank planes + row permutation
@@ -289,8 +298,12 @@ def run_product(args):
     try:
         bits = gsx.unpack_bitmap(outs[(args.steps - 1) % N_OUT_BUFFERS][:2048].cpu().numpy().view(np.uint32), N)
         B = min(2048, P)
-        first = bits.argmax(axis=1)
-        ok = bits[np.arange(B), first]
+        # bind target = a pseudo-random passing node per pod (kube-scheduler's pick is not part of the path)
+        cnt = bits.sum(axis=1)
+        ok = cnt > 0
+        pick = (np.arange(B, dtype=np.int64) * 2654435761 % np.maximum(cnt, 1))
+        csum = np.cumsum(bits, axis=1)
+        first = (csum > pick[:, None]).argmax(axis=1)
         binds = synth.bind_records(first[ok], reqs[:B][ok].view(np.int64), first_slot=sc.n_pods)
         snap.profile(True)
         snap.profile_reset()

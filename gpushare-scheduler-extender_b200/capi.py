@@ -17,7 +17,8 @@ NODE_OK, NODE_NOT_FOUND, NODE_NOT_SHARE = 0, 1, 2
 EV_ADD, EV_REMOVE = 0, 1
 POD_VALID, POD_COUNTED = 1, 2
 BIND_NO_DEVICE, BIND_NODE_NOT_FOUND = -1, -2
-MAX_DEVS, MAX_BATCH = 64, 16384
+MAX_DEVS, MAX_BATCH = 64, 12288
+STAGE_SORT, STAGE_NODE_RANK, STAGE_EXPAND = 1, 2, 4
 K_REBUILD, K_APPLY, K_SORT, K_NODE_RANK, K_EXPAND, K_BIND_SORT, K_BIND_SCAN = range(7)
 KERNEL_NAMES = ["rebuild", "apply", "sort", "node_rank", "expand", "bind_sort", "bind_scan"]
 
@@ -34,7 +35,7 @@ assert NODE_DT.itemsize == 24 and POD_DT.itemsize == 16 and EVENT_DT.itemsize ==
 EXPORTS = [
     "gs_last_error", "gs_abi_version", "gs_device_count", "gs_snapshot_create", "gs_snapshot_destroy",
     "gs_node_upsert", "gs_node_count", "gs_pods_load", "gs_rebuild", "gs_pods_apply", "gs_filter_batch",
-    "gs_filter_batch_device", "gs_node_classes", "gs_bind_batch", "gs_bind_rollback", "gs_inspect",
+    "gs_filter_batch_device", "gs_filter_stages_device", "gs_node_classes", "gs_bind_batch", "gs_bind_rollback", "gs_inspect",
     "gs_read_used", "gs_read_pods", "gs_host_alloc", "gs_host_free", "gs_profile_enable", "gs_profile_read",
     "gs_profile_reset", "gs_launch_count", "gs_device_ptrs",
 ]
@@ -78,6 +79,7 @@ def load():
         "gs_pods_apply": (C.c_int, [vp, vp, u32]),
         "gs_filter_batch": (C.c_int, [vp, vp, u32, vp, u32]),
         "gs_filter_batch_device": (C.c_int, [vp, vp, u32, vp, u32, vp]),
+        "gs_filter_stages_device": (C.c_int, [vp, u32, vp, u32, vp, u32, vp]),
         "gs_node_classes": (C.c_int, [vp, vp, u32]),
         "gs_bind_batch": (C.c_int, [vp, vp, u32, vp]),
         "gs_bind_rollback": (C.c_int, [vp, vp, u32]),
@@ -215,6 +217,11 @@ class Snapshot:
     def filter_batch_device(self, d_req_ptr: int, n_pods: int, d_out_ptr: int, row_stride_words: int, stream: int = 0):
         _check(load().gs_filter_batch_device(self.h, C.c_void_p(d_req_ptr), n_pods, C.c_void_p(d_out_ptr),
                                              row_stride_words, C.c_void_p(stream)))
+
+    def filter_stages_device(self, stage_mask: int, d_req_ptr: int, n_pods: int, d_out_ptr: int,
+                             row_stride_words: int, stream: int = 0):
+        _check(load().gs_filter_stages_device(self.h, stage_mask, C.c_void_p(d_req_ptr), n_pods, C.c_void_p(d_out_ptr),
+                                              row_stride_words, C.c_void_p(stream)))
 
     # ---- bind ----
     def bind_batch(self, binds: np.ndarray) -> np.ndarray:

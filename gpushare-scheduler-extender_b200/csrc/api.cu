@@ -136,25 +136,35 @@ uint32_t bitmap_words(const gs_snapshot* s) { return (s->n_nodes + 31u) / 32u; }
 
 // The three filter kernels for one chunk of <= GS_MAX_BATCH pods; everything on `st`.
 int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_out, uint32_t row_stride,
-                 cudaStream_t st) {
+                 cudaStream_t st, uint32_t stages = 7u) {
     const uint32_t words = bitmap_words(s);
     if (n_pods == 0 || words == 0) return GS_OK;
     const uint32_t words_pad = (words + gs::kTileWords - 1) / gs::kTileWords * gs::kTileWords;
     if (words_pad > s->rank_words) return fail(GS_ERR_CAPACITY, "rank planes too small");
-    int rc;
-    rc = timed(s, GS_K_SORT, st, 1, [&] {
-        return gs::launch_sort_requests(s->device, d_req, n_pods, s->d_sorted_keys, s->d_perm, st);
-    });
+    gs::FilterBuffers fb;
+    fb.grouped_req = s->d_sorted_keys;
+    fb.perm = s->d_perm;
+    fb.row_bucket = s->d_row_bucket;
+    fb.pod_slot = s->d_pod_slot;
+    fb.pod_hist = s->d_pod_hist;
+    fb.planes = s->d_rank_planes;
+    fb.node_key = s->d_node_key;
+    fb.sched = s->d_sched;
+    // bucket scale: requests up to the largest device capacity spread over all 512 buckets
+    uint32_t bits = 0;
+    while (bits < 64 && (s->max_capacity >> bits) != 0) ++bits;
+    const uint32_t shift = bits > 9 ? bits - 9 : 0;
+    int rc = GS_OK;
+    const bool do_pods = (stages & GS_STAGE_SORT) != 0, do_nodes = (stages & GS_STAGE_NODE_RANK) != 0;
+    if (do_pods || do_nodes)
+        rc = timed(s, do_pods ? GS_K_SORT : GS_K_NODE_RANK, st, do_pods ? 2 : 1, [&] {
+            return gs::launch_prep(d_req, n_pods, do_pods, do_nodes, shift, fb, s->d_used, s->d_cap, s->d_nodeinfo,
+                                   s->n_nodes, s->max_devs, words_pad, st);
+        });
     if (rc) return rc;
-    rc = timed(s, GS_K_NODE_RANK, st, 1, [&] {
-        return gs::launch_node_rank(s->d_used, s->d_cap, s->d_nodeinfo, s->n_nodes, s->max_devs, s->d_sorted_keys,
-                                    n_pods, s->d_rank_planes, words_pad, st);
-    });
-    if (rc) return rc;
-    rc = timed(s, GS_K_EXPAND, st, 1, [&] {
-        return gs::launch_expand(s->device, s->sm_count, s->d_rank_planes, s->d_perm, n_pods, words, row_stride,
-                                 d_out, st);
-    });
+    if (stages & GS_STAGE_EXPAND)
+        rc = timed(s, GS_K_EXPAND, st, 1,
+                   [&] { return gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, st); });
     return rc;
 }
 
@@ -229,6 +239,13 @@ int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32
     CU_NEW(cudaMalloc(&s->d_sorted_keys, (size_t)GS_MAX_BATCH * sizeof(u64)));
     CU_NEW(cudaMalloc(&s->d_perm, (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
     CU_NEW(cudaMalloc(&s->d_rank_planes, (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t)));
+    CU_NEW(cudaMalloc(&s->d_node_key, (size_t)s->rank_words * 32 * sizeof(u64)));
+    CU_NEW(cudaMalloc(&s->d_row_bucket, (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
+    CU_NEW(cudaMalloc(&s->d_pod_slot, (size_t)GS_MAX_BATCH * sizeof(uint32_t)));
+    CU_NEW(cudaMalloc(&s->d_pod_hist, 513 * sizeof(uint32_t)));
+    CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 513 * sizeof(uint32_t), s->stream));
+    CU_NEW(cudaMalloc(&s->d_sched, 2 * sizeof(uint32_t)));
+    CU_NEW(cudaMemsetAsync(s->d_sched, 0, 2 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_used, 0, (size_t)max_nodes * max_devs * sizeof(u64), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_cap, 0, (size_t)max_nodes * sizeof(u64), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_pods, 0, (size_t)max_pods * sizeof(gs_pod_record), s->stream));
@@ -254,6 +271,11 @@ int gs_snapshot_destroy(gs_snapshot* s) {
     cudaFree(s->d_sorted_keys);
     cudaFree(s->d_perm);
     cudaFree(s->d_rank_planes);
+    cudaFree(s->d_node_key);
+    cudaFree(s->d_row_bucket);
+    cudaFree(s->d_pod_slot);
+    cudaFree(s->d_pod_hist);
+    cudaFree(s->d_sched);
     cudaFree(s->d_stage);
     cudaFree(s->d_bitmap);
     if (s->h_stage) cudaFreeHost(s->h_stage);
@@ -283,6 +305,8 @@ int gs_node_upsert(gs_snapshot* s, const gs_node* nodes, uint32_t n) {
         if (nodes[i].node_class > GS_NODE_NOT_SHARE) return fail(GS_ERR_INVALID, "bad node_class");
         lo = std::min(lo, nodes[i].node_idx);
         hi = std::max(hi, nodes[i].node_idx);
+        if (nodes[i].node_class == GS_NODE_OK && nodes[i].dev_count > 0 && nodes[i].dev_capacity < (1ull << 40))
+            s->max_capacity = std::max<unsigned long long>(s->max_capacity, nodes[i].dev_capacity);
     }
     // Read-modify-write of the covered index range through pinned staging: two contiguous copies
     // each way whatever the order of `nodes` (bulk upserts are contiguous; single ones are tiny).
@@ -385,6 +409,18 @@ int gs_filter_batch_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pod
     if (rc) return rc;
     cudaStream_t st = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : s->stream;
     return filter_device_locked(s, reinterpret_cast<const u64*>(d_req), n_pods, d_out_bitmap, row_stride_words, st);
+}
+
+int gs_filter_stages_device(gs_snapshot* s, uint32_t stage_mask, const uint64_t* d_req, uint32_t n_pods,
+                            uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream) {
+    if (!s || !d_req || !d_out_bitmap) return fail(GS_ERR_INVALID, "null argument");
+    if (n_pods > GS_MAX_BATCH) return fail(GS_ERR_INVALID, "n_pods > GS_MAX_BATCH");
+    Guard g(s);
+    int rc = use_device(s);
+    if (rc) return rc;
+    if (row_stride_words < bitmap_words(s)) return fail(GS_ERR_INVALID, "row_stride_words too small");
+    cudaStream_t st = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : s->stream;
+    return filter_chunk(s, reinterpret_cast<const u64*>(d_req), n_pods, d_out_bitmap, row_stride_words, st, stage_mask);
 }
 
 int gs_filter_batch(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint32_t* out_bitmap,

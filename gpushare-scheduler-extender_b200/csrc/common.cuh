@@ -7,6 +7,7 @@
 #include <string>
 
 #include "gpushare_b200.h"
+#include "kernels.h"
 
 namespace gs {
 
@@ -18,10 +19,9 @@ __host__ __device__ inline uint32_t nodeinfo_class(uint32_t w) { return (w >> 16
 constexpr uint32_t kUnsetNodeinfo = (uint32_t)GS_NODE_NOT_FOUND << 16;
 
 // Filter geometry.
-constexpr int kRankPlanes = 16;          // bit planes per 32-node word of the rank array
+constexpr int kRankPlanes = 10;          // bit planes per 32-node word of the node bucket ids (0..513)
 constexpr int kTileRows = 64;            // sorted pod rows per tile
 constexpr int kTileWords = 128;          // 32-bit words (4096 nodes) per tile
-constexpr int kTileStride = kTileWords + 4;  // smem row stride in words (keeps 16 B alignment)
 constexpr int kExpandThreads = 256;
 
 struct ProfSlot {
@@ -49,7 +49,13 @@ struct gs_snapshot {
     int32_t* d_last_ev = nullptr;             // [max_pods], -1 when idle (K2)
     unsigned long long* d_sorted_keys = nullptr;  // [GS_MAX_BATCH] (K3/K4 sort output)
     uint16_t* d_perm = nullptr;               // [GS_MAX_BATCH] sorted position -> input index
-    uint32_t* d_rank_planes = nullptr;        // [rank_words][kRankPlanes] (K3)
+    uint16_t* d_row_bucket = nullptr;         // [GS_MAX_BATCH] (K3)
+    uint32_t* d_pod_slot = nullptr;           // [GS_MAX_BATCH] (K3)
+    uint32_t* d_pod_hist = nullptr;           // [513] (K3, self re-arming)
+    unsigned long long max_capacity = 0;      // largest dev_capacity of an OK node ever upserted (bucket scale)
+    uint32_t* d_rank_planes = nullptr;        // [rank_words / kTileWords][kRankPlanes][kTileWords] (K3)
+    unsigned long long* d_node_key = nullptr; // [rank_words * 32] (K3)
+    uint32_t* d_sched = nullptr;              // [2] tile scheduler of k_expand (self re-arming)
     uint32_t rank_words = 0;
     void* d_stage = nullptr;                  // generic device staging (events, binds, reqs, out)
     size_t d_stage_bytes = 0;

@@ -3,14 +3,17 @@
 //
 // The predicate for (pod p, node n) is   class[n]==OK  &&  ndev[n]>0  &&  max_d(cap[n]-used[n][d]) >= req[p]
 // (u64, wrapping subtraction: nodeinfo.go:260).  It is monotone in req[p], so with the pods sorted by
-// request every node's column is a step: ones for the first rank[n] sorted rows, zeros after, where
-// rank[n] = #{p : req[p] <= key[n]}.  Three kernels:
-//   k_radix_sort : one CTA sorts the (<=16384) requests, LSD radix on the bits that actually vary.
-//   k_node_rank  : per node, key = max available over its devices, rank = upper_bound(sorted req, key);
-//                  ranks are written bit-sliced (16 planes per 32-node word).
-//   k_expand     : writes the [P][N/32] bitmap, tile by tile, from the bit-sliced ranks.  One thread
-//                  turns 32 ranks into a word with 16 LOP3s; rows of a tile differ from the tile's base
-//                  word only in the few words that hold a step, which are patched in shared memory.
+// request every node's column is a step: ones up to the last request <= key[n], zeros after.  An exact
+// sort is not needed: it is enough to group the pods into narrow value buckets and settle the nodes
+// whose key falls inside a tile's own bucket range by direct comparison with each row's
+// request.  Three kernels:
+//   k_bucket_pods : one CTA groups the (<= GS_MAX_BATCH) requests into <= 512 value buckets.
+//   k_node_bucket : per node, key = max available over its devices and the bucket the key falls in,
+//                   bucket ids written bit-sliced (10 planes per 32-node word).
+//   k_expand      : writes the [P][N/32] bitmap tile by tile.  One thread turns the bucket ids of 32
+//                   nodes into a word with 10 LOP3s; only nodes whose bucket lies inside the tile's own
+//                   bucket range need the exact 64-bit comparison.
+// (k_radix_sort, a stable single-CTA LSD radix sort, orders the bind queue by node for K4.)
 #include "common.cuh"
 #include "kernels.h"
 
@@ -19,18 +22,20 @@ namespace gs {
 using u64 = unsigned long long;
 
 // ------------------------------------------------------------------------------------------------
-// single-CTA stable LSD radix sort of n <= GS_MAX_BATCH 64-bit keys (8-bit digits)
+// single-CTA stable LSD radix sort of n <= GS_MAX_BATCH 64-bit keys.  Only the bit span in which the
+// keys differ is sorted, in ceil(span / 9) passes of equal width (two 9-bit passes for MiB-sized
+// requests, eight 8-bit passes for arbitrary 64-bit keys).  Ranking inside a warp is the ballot
+// multi-split (one ballot per digit bit), per-warp counters, no atomics.
 // ------------------------------------------------------------------------------------------------
 constexpr int kSortThreads = 1024;
 constexpr int kSortWarps = kSortThreads / 32;
-constexpr int kSortMaxRounds = GS_MAX_BATCH / kSortThreads;  // 16 rounds of 32 keys per warp
+constexpr int kSortMaxRounds = GS_MAX_BATCH / kSortThreads;  // rounds of 32 keys per warp
+constexpr int kSortMaxBits = 9;
+constexpr int kSortBins = 1 << kSortMaxBits;
 constexpr size_t kSortSmemBytes = (size_t)GS_MAX_BATCH * 8 + (size_t)GS_MAX_BATCH * 2 * 2 +
-                                  256 * kSortWarps * 2 + 128 * 8;
+                                  (size_t)kSortBins * kSortWarps * 2 + kSortBins * 2 + 128 * 8;
+static_assert(GS_MAX_BATCH % kSortThreads == 0, "batch limit must be a whole number of rounds");
 
-struct ReqKeyLoader {
-    const u64* req;
-    __device__ u64 operator()(uint32_t i) const { return req[i]; }
-};
 struct BindKeyLoader {
     const gs_bind_req* binds;
     __device__ u64 operator()(uint32_t i) const { return (u64)binds[i].node_idx; }
@@ -43,8 +48,9 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
     u64* keys = reinterpret_cast<u64*>(smem_raw);
     uint16_t* idx_a = reinterpret_cast<uint16_t*>(keys + GS_MAX_BATCH);
     uint16_t* idx_b = idx_a + GS_MAX_BATCH;
-    uint16_t* hist = idx_b + GS_MAX_BATCH;  // [256 digits][32 warps]
-    u64* red = reinterpret_cast<u64*>(hist + 256 * kSortWarps);
+    uint16_t* hist = idx_b + GS_MAX_BATCH;            // [warp][bin]
+    uint16_t* bin_base = hist + kSortBins * kSortWarps;  // [bin]
+    u64* red = reinterpret_cast<u64*>(bin_base + kSortBins);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -80,54 +86,77 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
 
     uint16_t* src = idx_a;
     uint16_t* dst = idx_b;
-    const uint32_t rounds = (n + kSortThreads - 1) / kSortThreads;  // rounds of 32 keys per warp
-    const uint32_t chunk = rounds * 32;                             // consecutive positions per warp
-    const uint32_t lt_mask = (1u << lane) - 1u;
+    if (varying != 0) {
+        const int lo = __ffsll((long long)varying) - 1, hi = 63 - __clzll((long long)varying);
+        const int span = hi - lo + 1;
+        const int passes = (span + kSortMaxBits - 1) / kSortMaxBits;
+        const int bits = (span + passes - 1) / passes;
+        const uint32_t rounds = (n + kSortThreads - 1) / kSortThreads;
+        const uint32_t chunk = rounds * 32;  // consecutive positions per warp
+        const uint32_t lt_mask = (1u << lane) - 1u;
+        uint16_t* my_hist = hist + warp * kSortBins;
+        uint32_t* wsum = reinterpret_cast<uint32_t*>(red + 65);
 
-    for (int shift = 0; shift < 64; shift += 8) {
-        if (((varying >> shift) & 0xffull) == 0) continue;  // block-uniform: digit identical everywhere
-        for (uint32_t i = tid; i < 256 * kSortWarps; i += kSortThreads) hist[i] = 0;
-        __syncthreads();
+        for (int pass = 0; pass < passes; ++pass) {
+            const int shift = lo + pass * bits;
+            const int nb = min(bits, hi + 1 - shift);
+            const uint32_t nbins = 1u << nb, dmask = nbins - 1u;
 
-        // rank every key among the keys of its warp's chunk that share its digit
-        uint32_t slot[kSortMaxRounds];  // (digit << 16) | offset within (digit, warp)
+            for (uint32_t i = lane; i < kSortBins / 2; i += 32) reinterpret_cast<uint32_t*>(my_hist)[i] = 0;
+            __syncwarp();
+
+            // rank every key among the keys of its warp's chunk that share its digit
+            uint32_t slot[kSortMaxRounds];  // (digit << 16) | offset within (warp, digit)
 #pragma unroll
-        for (int r = 0; r < kSortMaxRounds; ++r) {
-            slot[r] = 0;
-            if ((uint32_t)r < rounds) {
-                const uint32_t pos = warp * chunk + r * 32 + lane;
-                const bool valid = pos < n;
-                uint32_t digit = 0x1ffu;
-                if (valid) digit = (uint32_t)(keys[src[pos]] >> shift) & 0xffu;
-                const uint32_t peers = __match_any_sync(0xffffffffu, digit);
-                const int leader = __ffs(peers) - 1;
-                uint32_t base = 0;
-                if ((int)lane == leader && valid) {
-                    base = hist[digit * kSortWarps + warp];
-                    hist[digit * kSortWarps + warp] = (uint16_t)(base + __popc(peers));
+            for (int r = 0; r < kSortMaxRounds; ++r) {
+                slot[r] = 0;
+                if ((uint32_t)r < rounds) {
+                    const uint32_t pos = warp * chunk + r * 32 + lane;
+                    const bool valid = pos < n;
+                    uint32_t digit = 0;
+                    if (valid) digit = (uint32_t)(keys[src[pos]] >> shift) & dmask;
+                    uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+                    for (int b = 0; b < kSortMaxBits; ++b) {
+                        if (b < nb) {
+                            const bool bit = (digit >> b) & 1u;
+                            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+                            peers &= bit ? bal : ~bal;
+                        }
+                    }
+                    uint32_t base = 0;
+                    int leader = 0;
+                    if (valid) {
+                        leader = __ffs(peers) - 1;
+                        if ((int)lane == leader) {
+                            base = my_hist[digit];
+                            my_hist[digit] = (uint16_t)(base + __popc(peers));
+                        }
+                    }
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    slot[r] = (digit << 16) | (base + __popc(peers & lt_mask));
+                    __syncwarp();
                 }
-                base = __shfl_sync(0xffffffffu, base, leader);
-                slot[r] = (digit << 16) | (base + __popc(peers & lt_mask));
-                __syncwarp();
             }
-        }
-        __syncthreads();
+            __syncthreads();
 
-        // exclusive scan of hist in (digit, warp) order: 8 consecutive counters per thread
-        {
-            uint4 raw = *reinterpret_cast<uint4*>(hist + tid * 8);
-            uint32_t c[8] = {raw.x & 0xffffu, raw.x >> 16, raw.y & 0xffffu, raw.y >> 16,
-                             raw.z & 0xffffu, raw.z >> 16, raw.w & 0xffffu, raw.w >> 16};
-            uint32_t sum = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) sum += c[i];
-            uint32_t incl = sum;
+            // per bin: exclusive prefix over warps (in place) and the bin total
+            uint32_t total = 0;
+            if (tid < nbins) {
+#pragma unroll 8
+                for (int w = 0; w < kSortWarps; ++w) {
+                    const uint32_t c = hist[w * kSortBins + tid];
+                    hist[w * kSortBins + tid] = (uint16_t)total;
+                    total += c;
+                }
+            }
+            // exclusive scan of the bin totals over the block
+            uint32_t incl = total;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
                 if ((int)lane >= o) incl += t;
             }
-            uint32_t* wsum = reinterpret_cast<uint32_t*>(red + 65);
             if (lane == 31) wsum[warp] = incl;
             __syncthreads();
             if (warp == 0) {
@@ -140,35 +169,24 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
                 wsum[lane] = wi - w;
             }
             __syncthreads();
-            uint32_t run = wsum[warp] + incl - sum;
-            uint32_t e[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                e[i] = run;
-                run += c[i];
-            }
-            raw.x = e[0] | (e[1] << 16);
-            raw.y = e[2] | (e[3] << 16);
-            raw.z = e[4] | (e[5] << 16);
-            raw.w = e[6] | (e[7] << 16);
-            *reinterpret_cast<uint4*>(hist + tid * 8) = raw;
-        }
-        __syncthreads();
+            if (tid < nbins) bin_base[tid] = (uint16_t)(wsum[warp] + incl - total);
+            __syncthreads();
 
 #pragma unroll
-        for (int r = 0; r < kSortMaxRounds; ++r) {
-            if ((uint32_t)r < rounds) {
-                const uint32_t pos = warp * chunk + r * 32 + lane;
-                if (pos < n) {
-                    const uint32_t digit = slot[r] >> 16, off = slot[r] & 0xffffu;
-                    dst[hist[digit * kSortWarps + warp] + off] = src[pos];
+            for (int r = 0; r < kSortMaxRounds; ++r) {
+                if ((uint32_t)r < rounds) {
+                    const uint32_t pos = warp * chunk + r * 32 + lane;
+                    if (pos < n) {
+                        const uint32_t digit = slot[r] >> 16, off = slot[r] & 0xffffu;
+                        dst[(uint32_t)bin_base[digit] + my_hist[digit] + off] = src[pos];
+                    }
                 }
             }
+            __syncthreads();
+            uint16_t* t = src;
+            src = dst;
+            dst = t;
         }
-        __syncthreads();
-        uint16_t* t = src;
-        src = dst;
-        dst = t;
     }
 
     for (uint32_t i = tid; i < n; i += kSortThreads) {
@@ -179,8 +197,26 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
 }
 
 // ------------------------------------------------------------------------------------------------
-// per-node key and rank, written as bit planes
+// k_prep: pod side and node side in one launch (independent roles chosen by blockIdx)
 // ------------------------------------------------------------------------------------------------
+// Values are mapped to kBuckets value buckets, bucket(x) = min(x >> shift, kBuckets - 1), with `shift`
+// derived on the host from the largest device capacity ever upserted, so requests up to that capacity
+// spread over all buckets; the last bucket is open-ended.  Bucket ids are stored 1-based.
+//
+// Pod blocks: first half of grouping the pending pods by bucket: every pod takes an arrival number in
+// its bucket with an L2 atomic.  k_group_pods then turns the bucket counts into offsets and writes the
+// grouped order.  Order inside a bucket is whatever the atomics give; the bitmap does not depend on it.
+//
+// Node blocks: one warp per 32-node word, lane = node.  key = max available memory over the node's
+// devices (nodeinfo.go:254-264, u64 wrap-around included) and
+//   q' = 0                                   class != OK or no devices (nodeinfo.go:123)
+//   q' = 1 + min(key >> shift, kBuckets)     otherwise
+// so that for a closed bucket b'  q' > b' implies key >= every request in it and q' < b' implies
+// key < all of them.  q' is written bit-sliced, plane-major inside blocks of kTileWords words:
+//   planes[((word / kTileWords) * kRankPlanes + k) * kTileWords + word % kTileWords] = bit k of 32 q'.
+constexpr int kPrepThreads = 512;
+constexpr uint32_t kBuckets = 512;
+
 __device__ __forceinline__ u64 node_key_generic(const u64* __restrict__ used_row, u64 cap, uint32_t ndev) {
     u64 key = 0;
     for (uint32_t d = 0; d < ndev; ++d) {
@@ -190,60 +226,123 @@ __device__ __forceinline__ u64 node_key_generic(const u64* __restrict__ used_row
     return key;
 }
 
-// One warp per 32-node word; lane = node.
 template <int kDevStride>
-__global__ void __launch_bounds__(256)
-k_node_rank(const u64* __restrict__ used, const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
-            uint32_t n_nodes, uint32_t dev_stride, const u64* __restrict__ sorted_req, uint32_t n_pods,
-            uint32_t* __restrict__ planes, uint32_t n_words) {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t word = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+__global__ void __launch_bounds__(kPrepThreads)
+k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32_t shift, FilterBuffers fb,
+       const u64* __restrict__ used, const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
+       uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words) {
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x < pod_blocks) {
+        // ---------------- pod role ----------------
+        uint32_t* ghist = fb.pod_hist;        // [kBuckets] + [1] finished-blocks counter
+        uint32_t* slots = fb.pod_slot;        // [GS_MAX_BATCH] (bucket << 16) | arrival number
+        const uint32_t i = blockIdx.x * kPrepThreads + tid;
+        if (i < n_pods) {
+            const u64 r = req[i];
+            const u64 bq = r >> shift;
+            const uint32_t b = bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1;
+            slots[i] = (b << 16) | atomicAdd(&ghist[b], 1u);
+        }
+        return;
+    }
+    // ---------------- node role ----------------
+    const uint32_t word = (blockIdx.x - pod_blocks) * (kPrepThreads / 32) + warp;
     if (word >= n_words) return;
     const uint32_t node = word * 32 + lane;
-    uint32_t rank = 0;
+    uint32_t q = 0;
+    u64 key = 0;
     if (node < n_nodes) {
         const uint32_t info = nodeinfo[node];
         const uint32_t ndev = nodeinfo_ndev(info);
         if (nodeinfo_class(info) == GS_NODE_OK && ndev > 0) {
             const u64 c = cap[node];
-            u64 key = 0;
             if (kDevStride == 8) {
                 const ulonglong2* row = reinterpret_cast<const ulonglong2*>(used + (size_t)node * 8);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    ulonglong2 u = row[q];
+                for (int k = 0; k < 4; ++k) {
+                    ulonglong2 u = row[k];
                     u64 a0 = c - u.x, a1 = c - u.y;
-                    if ((uint32_t)(2 * q) < ndev) key = a0 > key ? a0 : key;
-                    if ((uint32_t)(2 * q + 1) < ndev) key = a1 > key ? a1 : key;
+                    if ((uint32_t)(2 * k) < ndev) key = a0 > key ? a0 : key;
+                    if ((uint32_t)(2 * k + 1) < ndev) key = a1 > key ? a1 : key;
                 }
             } else {
                 key = node_key_generic(used + (size_t)node * dev_stride, c, ndev);
             }
-            // upper_bound: number of sorted requests <= key
-            uint32_t lo = 0, hi = n_pods;
-            while (lo < hi) {
-                uint32_t mid = (lo + hi) >> 1;
-                if (__ldg(sorted_req + mid) <= key)
-                    lo = mid + 1;
-                else
-                    hi = mid;
-            }
-            rank = lo;
+            const u64 bq = key >> shift;
+            q = 1u + (uint32_t)(bq < kBuckets ? bq : kBuckets);
         }
     }
+    fb.node_key[node] = key;
     uint32_t mine = 0;
 #pragma unroll
     for (int k = 0; k < kRankPlanes; ++k) {
-        uint32_t b = __ballot_sync(0xffffffffu, (rank >> k) & 1u);
+        uint32_t b = __ballot_sync(0xffffffffu, (q >> k) & 1u);
         if ((int)lane == k) mine = b;
     }
-    if (lane < kRankPlanes) planes[(size_t)word * kRankPlanes + lane] = mine;
+    if (lane < kRankPlanes)
+        fb.planes[((size_t)(word / kTileWords) * kRankPlanes + lane) * kTileWords + (word % kTileWords)] = mine;
+}
+
+// Second half of the pod side: bucket counts -> offsets (every block scans the 512 counts itself),
+// then each block writes the grouped position of its own pods.  The last block out re-arms the counts.
+__global__ void __launch_bounds__(kPrepThreads)
+k_group_pods(const u64* __restrict__ req, uint32_t n_pods, FilterBuffers fb) {
+    __shared__ uint32_t base[kBuckets];
+    __shared__ uint32_t wsum[kPrepThreads / 32];
+    __shared__ bool is_last;
+    static_assert(kPrepThreads == (int)kBuckets, "one bucket per thread in the scan");
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t* ghist = fb.pod_hist;
+    const uint32_t p = blockIdx.x * kPrepThreads + tid;
+    uint32_t sl = 0;
+    u64 r = 0;
+    if (p < n_pods) {
+        sl = fb.pod_slot[p];
+        r = req[p];
+    }
+    const uint32_t cnt = ghist[tid];
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane >= o) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = lane < kPrepThreads / 32 ? wsum[lane] : 0u;
+        uint32_t wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+            if ((int)lane >= o) wi += t;
+        }
+        if (lane < kPrepThreads / 32) wsum[lane] = wi - w;
+    }
+    __syncthreads();
+    base[tid] = wsum[warp] + incl - cnt;
+    __syncthreads();
+    if (p < n_pods) {
+        const uint32_t b = sl >> 16;
+        const uint32_t j = base[b] + (sl & 0xffffu);
+        fb.perm[j] = (uint16_t)p;
+        fb.grouped_req[j] = r;
+        fb.row_bucket[j] = (uint16_t)(b + 1);
+    }
+    // every block has read the counts once it is here; the last one out clears them
+    __syncthreads();
+    if (tid == 0) is_last = atomicAdd(&ghist[kBuckets], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (is_last) {
+        ghist[tid] = 0;
+        if (tid == 0) ghist[kBuckets] = 0;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
 // bitmap expansion
 // ------------------------------------------------------------------------------------------------
-// bit b of the result = (rank of node b >= t), ranks given as bit planes a[0..15] (LSB first)
+// bit b of the result = (q' of node b >= t), q' given as bit planes a[0..kRankPlanes) (LSB first)
 __device__ __forceinline__ uint32_t planes_ge(const uint32_t (&a)[kRankPlanes], uint32_t t) {
     uint32_t ge = 0xffffffffu;
 #pragma unroll
@@ -254,101 +353,211 @@ __device__ __forceinline__ uint32_t planes_ge(const uint32_t (&a)[kRankPlanes], 
     return ge;
 }
 
+// A tile is kTileRows consecutive grouped pods x kTileWords words (4096 nodes); its rows span request
+// buckets [bmin, bmax].  A node with q' > bmax passes in every row (base word), one with q' < bmin in
+// none; only nodes with bmin <= q' <= bmax need the exact 64-bit comparison key >= req per row.  Words
+// holding such nodes are recomputed row by row into a small shared-memory patch (a few such nodes:
+// lane = row, keys in registers; many: lane = node, one ballot per row); every other word goes from
+// registers straight to global memory.  Stores are 16 bytes per lane, 512 contiguous bytes per warp.
+constexpr uint32_t kPatchWords = 3072;  // patch capacity in 32-bit words (rows x patched words per sub-pass)
+constexpr int kSparseMax = 4;           // up to this many compared nodes a word takes the lane = row path
+constexpr int kDenseRows = 8;           // rows per unrolled step of the lane = node path
+
 struct ExpandSmem {
-    uint32_t tile[kTileRows * kTileStride];
-    uint32_t planes[kTileWords * kRankPlanes];
-    uint32_t basew[kTileWords];
-    uint32_t row_of[kTileRows];
-    uint32_t plist[kTileWords];
-    uint32_t n_partial;
+    uint32_t patch[kPatchWords];
+    u64 req[kTileRows + kDenseRows];    // requests of the tile's rows (+ padding read by the unrolled loop)
+    u64 ekey[kTileWords * kSparseMax];  // keys of the compared nodes of sparse words
+    uint32_t ebits[kTileWords];         // their bit positions, 8 bits each (0xff = unused)
+    uint32_t basew[kTileWords];         // nodes passing in every row
+    uint32_t somew[kTileWords];         // nodes that can pass in some row (q' >= bmin)
+    uint32_t row_of[kTileRows];         // output row (pod index) of every tile row
+    uint8_t plist[kTileWords];          // words to patch
+    uint8_t pidx[kTileWords];           // position in plist, 0xff = not patched
+    uint32_t n_partial, tile;
 };
 
 template <bool kVec>
 __global__ void __launch_bounds__(kExpandThreads)
-k_expand(const uint32_t* __restrict__ planes, const uint16_t* __restrict__ perm, uint32_t n_pods,
-         uint32_t words_out, uint32_t row_stride, uint32_t* __restrict__ out, uint32_t n_col_blocks,
-         uint32_t n_tiles) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    ExpandSmem& sm = *reinterpret_cast<ExpandSmem*>(smem_raw);
+k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_stride, uint32_t* __restrict__ out,
+         uint32_t n_col_blocks, uint32_t n_tiles) {
+    __shared__ __align__(16) ExpandSmem sm;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr uint32_t kWarps = kExpandThreads / 32;
+    static_assert(kExpandThreads >= kTileWords + kTileRows, "phase A: one thread per word, one per row");
+    const uint32_t* __restrict__ planes = fb.planes;
+    const u64* __restrict__ node_key = fb.node_key;
 
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    // dynamic tile scheduler; the ticket for the next tile is taken while the current one is processed
+    uint32_t ticket = 0;
+    if (tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);
+    for (;;) {
+        if (tid == 0) {
+            sm.tile = ticket;
+            sm.n_partial = 0;
+        }
+        __syncthreads();
+        if (sm.tile >= n_tiles) break;
+        if (tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);
+        const uint32_t tile = n_tiles - 1u - sm.tile;  // high buckets first: that is where node keys cluster
         const uint32_t rt = tile / n_col_blocks, cb = tile - rt * n_col_blocks;
         const uint32_t j0 = rt * kTileRows;
         const uint32_t rows = min((uint32_t)kTileRows, n_pods - j0);
-        const uint32_t j1 = j0 + rows;
         const uint32_t w0 = cb * kTileWords;
 
-        if (tid == 0) sm.n_partial = 0;
-        __syncthreads();
-
-        // A: one thread per word: base word (nodes whose step lies at or beyond the tile's last row)
-        //    and the list of words that hold a step inside the tile
+        // A: one thread per word (threads 0..127), one per row (threads 128..191)
         if (tid < kTileWords) {
             uint32_t a[kRankPlanes];
-            const uint4* src = reinterpret_cast<const uint4*>(planes + (size_t)(w0 + tid) * kRankPlanes);
+            const uint32_t* src = planes + (size_t)cb * kRankPlanes * kTileWords + tid;
 #pragma unroll
-            for (int q = 0; q < kRankPlanes / 4; ++q) {
-                uint4 v = __ldg(src + q);
-                a[4 * q] = v.x;
-                a[4 * q + 1] = v.y;
-                a[4 * q + 2] = v.z;
-                a[4 * q + 3] = v.w;
-                *reinterpret_cast<uint4*>(&sm.planes[tid * kRankPlanes + 4 * q]) = v;
-            }
-            const uint32_t all_rows = planes_ge(a, j1);     // rank >= j1: set in every row of the tile
-            const uint32_t some_rows = planes_ge(a, j0 + 1);  // rank >  j0: set in the first row at least
+            for (int k = 0; k < kRankPlanes; ++k) a[k] = __ldg(src + k * kTileWords);
+            const uint32_t bmin = fb.row_bucket[j0], bmax = fb.row_bucket[j0 + rows - 1];
+            // the last bucket is open-ended: no node is known to cover all of it
+            const uint32_t t_all = bmax == kBuckets ? kBuckets + 2u : bmax + 1u;
+            const uint32_t all_rows = planes_ge(a, t_all);
+            const uint32_t some_rows = planes_ge(a, bmin);
             sm.basew[tid] = all_rows;
-            if (some_rows & ~all_rows) sm.plist[atomicAdd(&sm.n_partial, 1u)] = tid;
+            sm.somew[tid] = some_rows;
+            uint32_t pm = some_rows & ~all_rows;
+            uint8_t pi = 0xff;
+            if (pm) {
+                pi = (uint8_t)atomicAdd(&sm.n_partial, 1u);
+                sm.plist[pi] = (uint8_t)tid;
+                if (__popc(pm) <= kSparseMax) {
+                    const u64* keys = node_key + (size_t)(w0 + tid) * 32;
+                    uint32_t eb = 0xffffffffu;
+                    u64 kk[kSparseMax];
+#pragma unroll
+                    for (int i = 0; i < kSparseMax; ++i) {
+                        kk[i] = 0;
+                        if (pm) {
+                            const uint32_t bit = __ffs(pm) - 1;
+                            pm &= pm - 1;
+                            kk[i] = __ldg(keys + bit);
+                            eb = (eb & ~(0xffu << (8 * i))) | (bit << (8 * i));
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < kSparseMax; ++i) sm.ekey[tid * kSparseMax + i] = kk[i];
+                    sm.ebits[tid] = eb;
+                }
+            }
+            sm.pidx[tid] = pi;
         } else if (tid < kTileWords + kTileRows) {
             const uint32_t r = tid - kTileWords;
-            sm.row_of[r] = r < rows ? (uint32_t)perm[j0 + r] : 0u;
-        }
-        __syncthreads();
-
-        // B: fill the tile with the base words
-        {
-            const uint4 b4 = *reinterpret_cast<const uint4*>(&sm.basew[lane * 4]);
-            for (uint32_t r = warp; r < rows; r += kWarps)
-                *reinterpret_cast<uint4*>(&sm.tile[r * kTileStride + lane * 4]) = b4;
-        }
-        __syncthreads();
-
-        // C: words with a step inside the tile: lane = row, exact word from the planes
-        {
-            const uint32_t np = sm.n_partial;
-            for (uint32_t k = warp; k < np; k += kWarps) {
-                const uint32_t t = sm.plist[k];
-                uint32_t a[kRankPlanes];
-#pragma unroll
-                for (int q = 0; q < kRankPlanes; ++q) a[q] = sm.planes[t * kRankPlanes + q];
-                for (uint32_t r = lane; r < rows; r += 32)
-                    sm.tile[r * kTileStride + t] = planes_ge(a, j0 + r + 1);
+            if (r < rows) {
+                sm.row_of[r] = (uint32_t)fb.perm[j0 + r];
+                sm.req[r] = fb.grouped_req[j0 + r];
+            } else {
+                sm.req[r] = ~0ull;
             }
+        } else if (tid < kTileWords + kTileRows + kDenseRows) {
+            sm.req[tid - kTileWords] = ~0ull;
         }
         __syncthreads();
 
-        // D: rows go to their pods' rows of the output
-        if (kVec) {
-            const uint32_t wcol = w0 + lane * 4;
-            if (wcol < words_out) {
-                for (uint32_t r = warp; r < rows; r += kWarps) {
-                    const uint4 v = *reinterpret_cast<const uint4*>(&sm.tile[r * kTileStride + lane * 4]);
-                    __stcs(reinterpret_cast<uint4*>(out + (size_t)sm.row_of[r] * row_stride + wcol), v);
+        const uint32_t np = sm.n_partial;
+        // rows per sub-pass so that np patched words x rows fit the patch (odd stride spreads banks)
+        uint32_t pstride = np ? kPatchWords / np : kPatchWords;
+        pstride -= (pstride & 1u) ^ 1u;
+        const uint32_t sub_rows = min((uint32_t)kTileRows, pstride);
+        for (uint32_t r0 = 0; r0 < rows; r0 += sub_rows) {
+            const uint32_t rcount = min(sub_rows, rows - r0);
+            // C: patched words
+            if (np) {
+                u64 nextkey = 0;
+                {
+                    const uint32_t t = warp < np ? sm.plist[warp] : 0u;
+                    nextkey = __ldg(node_key + (size_t)(w0 + t) * 32 + lane);
+                }
+                for (uint32_t k = warp; k < np; k += kWarps) {
+                    const uint32_t t = sm.plist[k];
+                    const uint32_t base = sm.basew[t], some = sm.somew[t];
+                    const u64 mykey = nextkey;
+                    if (k + kWarps < np)  // prefetch the next word's keys for the lane = node path
+                        nextkey = __ldg(node_key + (size_t)(w0 + sm.plist[k + kWarps]) * 32 + lane);
+                    uint32_t* prow = &sm.patch[k * pstride];
+                    if (__popc(some & ~base) <= kSparseMax) {
+                        // lane = row; the compared nodes' keys come from shared memory
+                        const uint32_t eb = sm.ebits[t];
+                        u64 kk[kSparseMax];
+                        uint32_t kb[kSparseMax];
+#pragma unroll
+                        for (int i = 0; i < kSparseMax; ++i) {
+                            const uint32_t bit = (eb >> (8 * i)) & 0xffu;
+                            kk[i] = sm.ekey[t * kSparseMax + i];
+                            kb[i] = bit == 0xffu ? 0u : 1u << bit;
+                        }
+                        for (uint32_t rr = lane; rr < rcount; rr += 32) {
+                            const u64 rq = sm.req[r0 + rr];
+                            uint32_t v = base;
+#pragma unroll
+                            for (int i = 0; i < kSparseMax; ++i)
+                                if (kk[i] >= rq) v |= kb[i];  // unused slots have kb == 0
+                            prow[rr] = v;
+                        }
+                    } else {
+                        // lane = node; one ballot per row, kDenseRows rows per step.  Masking with `some`
+                        // clears the nodes that can never pass (q' == 0 stores key 0, which would match
+                        // a zero request).
+                        for (uint32_t g = 0; g < rcount; g += kDenseRows) {
+                            uint32_t mine = 0;
+#pragma unroll
+                            for (int i = 0; i < kDenseRows; ++i) {
+                                const u64 rq = sm.req[r0 + g + i];
+                                const uint32_t bal = __ballot_sync(0xffffffffu, mykey >= rq) & some;
+                                if ((int)lane == i) mine = bal;
+                            }
+                            if (lane < kDenseRows && g + lane < rcount) prow[g + lane] = mine;
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+            // D: lane owns 4 words, warp owns rows r0 + warp, r0 + warp + kWarps, ...
+            if (kVec) {
+                const uint32_t wcol = w0 + lane * 4;
+                if (wcol < words_out) {
+                    const uint4 b4 = *reinterpret_cast<const uint4*>(&sm.basew[lane * 4]);
+                    const uint32_t p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lane * 4]);
+                    uint32_t* dst = out + wcol;
+                    if (p4 == 0xffffffffu) {
+                        for (uint32_t rr = warp; rr < rcount; rr += kWarps)
+                            __stcs(reinterpret_cast<uint4*>(dst + (size_t)sm.row_of[r0 + rr] * row_stride), b4);
+                    } else {
+                        const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
+                        for (uint32_t rr = warp; rr < rcount; rr += kWarps) {
+                            uint4 v = b4;
+                            if (k0 != 0xffu) v.x = sm.patch[k0 * pstride + rr];
+                            if (k1 != 0xffu) v.y = sm.patch[k1 * pstride + rr];
+                            if (k2 != 0xffu) v.z = sm.patch[k2 * pstride + rr];
+                            if (k3 != 0xffu) v.w = sm.patch[k3 * pstride + rr];
+                            __stcs(reinterpret_cast<uint4*>(dst + (size_t)sm.row_of[r0 + rr] * row_stride), v);
+                        }
+                    }
+                }
+            } else {
+                for (uint32_t rr = warp; rr < rcount; rr += kWarps) {
+                    uint32_t* dst = out + (size_t)sm.row_of[r0 + rr] * row_stride + w0;
+#pragma unroll
+                    for (int c = 0; c < kTileWords / 32; ++c) {
+                        const uint32_t wl = c * 32 + lane;
+                        if (w0 + wl < words_out) {
+                            const uint32_t k = sm.pidx[wl];
+                            __stcs(dst + wl, k != 0xffu ? sm.patch[k * pstride + rr] : sm.basew[wl]);
+                        }
+                    }
                 }
             }
-        } else {
-            for (uint32_t r = warp; r < rows; r += kWarps) {
-                uint32_t* dst = out + (size_t)sm.row_of[r] * row_stride;
-#pragma unroll
-                for (int c = 0; c < kTileWords / 32; ++c) {
-                    const uint32_t wl = c * 32 + lane;
-                    if (w0 + wl < words_out) __stcs(dst + w0 + wl, sm.tile[r * kTileStride + wl]);
-                }
-            }
+            if (np && r0 + sub_rows < rows) __syncthreads();  // the next sub-pass overwrites the patch
         }
-        __syncthreads();
+    }
+    // the last CTA out re-arms the scheduler for the next launch
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(&fb.sched[1], 1u) == gridDim.x - 1) {
+            fb.sched[0] = 0;
+            fb.sched[1] = 0;
+        }
     }
 }
 
@@ -359,28 +568,11 @@ static bool g_attr_done[64] = {};
 
 static cudaError_t ensure_attrs(int device) {
     if (device >= 0 && device < 64 && g_attr_done[device]) return cudaSuccess;
-    cudaError_t e;
-    e = cudaFuncSetAttribute(k_radix_sort<ReqKeyLoader>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)kSortSmemBytes);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_radix_sort<BindKeyLoader>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)kSortSmemBytes);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_expand<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ExpandSmem));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_expand<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ExpandSmem));
+    cudaError_t e = cudaFuncSetAttribute(k_radix_sort<BindKeyLoader>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)kSortSmemBytes);
     if (e != cudaSuccess) return e;
     if (device >= 0 && device < 64) g_attr_done[device] = true;
     return cudaSuccess;
-}
-
-cudaError_t launch_sort_requests(int device, const u64* d_req, uint32_t n, u64* d_sorted, uint16_t* d_perm,
-                                 cudaStream_t st) {
-    cudaError_t e = ensure_attrs(device);
-    if (e != cudaSuccess) return e;
-    ReqKeyLoader ld{d_req};
-    k_radix_sort<ReqKeyLoader><<<1, kSortThreads, kSortSmemBytes, st>>>(ld, n, d_sorted, d_perm);
-    return cudaGetLastError();
 }
 
 cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n, u64* d_sorted,
@@ -392,41 +584,39 @@ cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n
     return cudaGetLastError();
 }
 
-cudaError_t launch_node_rank(const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo, uint32_t n_nodes,
-                             uint32_t dev_stride, const u64* d_sorted, uint32_t n_pods, uint32_t* d_planes,
-                             uint32_t n_words, cudaStream_t st) {
-    const uint32_t threads = 256;
-    const uint32_t blocks = (n_words * 32 + threads - 1) / threads;
-    if (blocks == 0) return cudaSuccess;
+cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do_nodes, uint32_t shift,
+                        const FilterBuffers& fb, const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo,
+                        uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, cudaStream_t st) {
+    const uint32_t pod_blocks = do_pods ? (n_pods + kPrepThreads - 1) / kPrepThreads : 0u;
+    const uint32_t node_blocks = do_nodes ? (n_words + kPrepThreads / 32 - 1) / (kPrepThreads / 32) : 0u;
+    if (pod_blocks + node_blocks == 0) return cudaSuccess;
     if (dev_stride == 8)
-        k_node_rank<8><<<blocks, threads, 0, st>>>(d_used, d_cap, d_nodeinfo, n_nodes, dev_stride, d_sorted,
-                                                    n_pods, d_planes, n_words);
+        k_prep<8><<<pod_blocks + node_blocks, kPrepThreads, 0, st>>>(d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap,
+                                                                     d_nodeinfo, n_nodes, dev_stride, n_words);
     else
-        k_node_rank<0><<<blocks, threads, 0, st>>>(d_used, d_cap, d_nodeinfo, n_nodes, dev_stride, d_sorted,
-                                                    n_pods, d_planes, n_words);
+        k_prep<0><<<pod_blocks + node_blocks, kPrepThreads, 0, st>>>(d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap,
+                                                                     d_nodeinfo, n_nodes, dev_stride, n_words);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess || pod_blocks == 0) return e;
+    k_group_pods<<<pod_blocks, kPrepThreads, 0, st>>>(d_req, n_pods, fb);
     return cudaGetLastError();
 }
 
-cudaError_t launch_expand(int device, int sm_count, const uint32_t* d_planes, const uint16_t* d_perm,
-                          uint32_t n_pods, uint32_t words, uint32_t row_stride, uint32_t* d_out,
-                          cudaStream_t st) {
-    cudaError_t e = ensure_attrs(device);
-    if (e != cudaSuccess) return e;
+cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
+                          uint32_t row_stride, uint32_t* d_out, cudaStream_t st) {
     if (n_pods == 0 || words == 0) return cudaSuccess;
     const bool vec = (row_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_out) & 15u) == 0);
     const uint32_t words_out = vec ? ((words + 3u) & ~3u) : words;
     const uint32_t n_col_blocks = (words_out + kTileWords - 1) / kTileWords;
     const uint32_t n_row_tiles = (n_pods + kTileRows - 1) / kTileRows;
     const uint32_t n_tiles = n_col_blocks * n_row_tiles;
-    const uint32_t per_sm = 4;
+    const uint32_t per_sm = 6;  // resident CTAs per SM (256 threads, ~20 KB shared each)
     uint32_t grid = (uint32_t)sm_count * per_sm;
     if (grid > n_tiles) grid = n_tiles;
     if (vec)
-        k_expand<true><<<grid, kExpandThreads, sizeof(ExpandSmem), st>>>(d_planes, d_perm, n_pods, words_out,
-                                                                         row_stride, d_out, n_col_blocks, n_tiles);
+        k_expand<true><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, n_tiles);
     else
-        k_expand<false><<<grid, kExpandThreads, sizeof(ExpandSmem), st>>>(d_planes, d_perm, n_pods, words_out,
-                                                                          row_stride, d_out, n_col_blocks, n_tiles);
+        k_expand<false><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, n_tiles);
     return cudaGetLastError();
 }
 

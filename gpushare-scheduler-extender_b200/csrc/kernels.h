@@ -8,16 +8,24 @@
 namespace gs {
 
 // K3 (filter_kernels.cu)
-cudaError_t launch_sort_requests(int device, const unsigned long long* d_req, uint32_t n,
-                                 unsigned long long* d_sorted, uint16_t* d_perm, cudaStream_t st);
+struct FilterBuffers {              // work buffers of one filter launch sequence (HBM scratch)
+    unsigned long long* grouped_req;  // [GS_MAX_BATCH] requests in bucket order
+    uint16_t* perm;                   // [GS_MAX_BATCH] grouped position -> pod index
+    uint16_t* row_bucket;             // [GS_MAX_BATCH] 1-based bucket of every grouped row
+    uint32_t* pod_slot;               // [GS_MAX_BATCH] (bucket << 16) | arrival number
+    uint32_t* pod_hist;               // [512 + 1] bucket counts + finished-blocks counter (self re-arming)
+    uint32_t* planes;                 // [words / kTileWords][kRankPlanes][kTileWords] node bucket ids, bit-sliced
+    unsigned long long* node_key;     // [words * 32] max available memory per node
+    uint32_t* sched;                  // [2] tile scheduler of k_expand (self re-arming)
+};
 cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n, unsigned long long* d_sorted,
                               uint16_t* d_perm, cudaStream_t st);
-cudaError_t launch_node_rank(const unsigned long long* d_used, const unsigned long long* d_cap,
-                             const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride,
-                             const unsigned long long* d_sorted, uint32_t n_pods, uint32_t* d_planes,
-                             uint32_t n_words, cudaStream_t st);
-cudaError_t launch_expand(int device, int sm_count, const uint32_t* d_planes, const uint16_t* d_perm,
-                          uint32_t n_pods, uint32_t words, uint32_t row_stride, uint32_t* d_out, cudaStream_t st);
+cudaError_t launch_prep(const unsigned long long* d_req, uint32_t n_pods, bool do_pods, bool do_nodes, uint32_t shift,
+                        const FilterBuffers& fb, const unsigned long long* d_used, const unsigned long long* d_cap,
+                        const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words,
+                        cudaStream_t st);
+cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
+                          uint32_t row_stride, uint32_t* d_out, cudaStream_t st);
 
 // K1 / K2 / K4 (state_kernels.cu)
 cudaError_t launch_validate_records(gs_pod_record* d_pods, uint32_t first, uint32_t n, const uint32_t* d_nodeinfo,

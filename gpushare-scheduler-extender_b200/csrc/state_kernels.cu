@@ -155,6 +155,9 @@ __global__ void k_events_apply(const gs_pod_event* __restrict__ ev, uint32_t n, 
 // first bind of a node walks that node's binds in order: allocateGPUID (nodeinfo.go:209-252) then the
 // commit of Allocate (nodeinfo.go:190-203).
 // ------------------------------------------------------------------------------------------------
+// kRegs: the node's used[] row lives in registers (stride-8 snapshots) for the whole walk and is written
+// back once; otherwise the walk reads and writes the row in global memory.
+template <bool kRegs>
 __global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, const u64* __restrict__ sorted_nodes,
                             const uint16_t* __restrict__ perm, gs_pod_record* pods, uint32_t max_pods,
                             const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, const u64* __restrict__ cap,
@@ -168,6 +171,16 @@ __global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, c
     const uint32_t ndev = known ? nodeinfo_ndev(nodeinfo[node]) : 0u;
     const u64 c = known ? cap[node] : 0ull;
     u64* row = used + (size_t)node * dev_stride;
+    u64 reg[8];
+    if (kRegs && known) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            ulonglong2 v = reinterpret_cast<const ulonglong2*>(row)[q];
+            reg[2 * q] = v.x;
+            reg[2 * q + 1] = v.y;
+        }
+    }
+    bool dirty = false;
     for (uint32_t k = j; k < n && sorted_nodes[k] == node64; ++k) {
         const uint32_t bi = perm[k];
         const gs_bind_req b = binds[bi];
@@ -178,10 +191,19 @@ __global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, c
         int cand = -1;
         u64 cand_mem = 0;
         if (b.req > 0) {
-            for (uint32_t d = 0; d < ndev; ++d) {
-                const u64 avail = c - row[d];
-                if (avail >= b.req) {
-                    if (cand == -1 || cand_mem > avail) {
+            if (kRegs) {
+#pragma unroll
+                for (int d = 0; d < 8; ++d) {
+                    const u64 avail = c - reg[d];
+                    if ((uint32_t)d < ndev && avail >= b.req && (cand == -1 || cand_mem > avail)) {
+                        cand = d;
+                        cand_mem = avail;
+                    }
+                }
+            } else {
+                for (uint32_t d = 0; d < ndev; ++d) {
+                    const u64 avail = c - row[d];
+                    if (avail >= b.req && (cand == -1 || cand_mem > avail)) {
                         cand = (int)d;
                         cand_mem = avail;
                     }
@@ -192,10 +214,19 @@ __global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, c
         if (cand >= 0 && b.slot < max_pods) {
             gs_pod_record old = load_record(pods + b.slot);
             if ((old.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED) && old.mem) {
-                if (old.node_idx == node)
-                    row[old.dev] -= old.mem;  // same UID re-added on this node: replace, do not double count
-                else
+                // the slot already held an entry (same UID bound again): replace, do not double count
+                if (old.node_idx == node) {
+                    if (kRegs) {
+#pragma unroll
+                        for (int d = 0; d < 8; ++d)
+                            if (d == old.dev) reg[d] -= old.mem;
+                        dirty = true;
+                    } else {
+                        row[old.dev] -= old.mem;
+                    }
+                } else {
                     atomicAdd(&used[(size_t)old.node_idx * dev_stride + (uint32_t)old.dev], 0ull - old.mem);
+                }
             }
             gs_pod_record now;
             now.mem = b.commit_mem;
@@ -204,8 +235,21 @@ __global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, c
             now.flags = (uint8_t)(GS_POD_VALID | (b.counted ? GS_POD_COUNTED : 0u));
             now.pad_ = 0;
             store_record(pods + b.slot, now);
-            if (b.counted) row[cand] += b.commit_mem;
+            if (b.counted) {
+                if (kRegs) {
+#pragma unroll
+                    for (int d = 0; d < 8; ++d)
+                        if (d == cand) reg[d] += b.commit_mem;
+                    dirty = true;
+                } else {
+                    row[cand] += b.commit_mem;
+                }
+            }
         }
+    }
+    if (kRegs && dirty) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) reinterpret_cast<ulonglong2*>(row)[q] = make_ulonglong2(reg[2 * q], reg[2 * q + 1]);
     }
 }
 
@@ -246,8 +290,12 @@ cudaError_t launch_bind_scan(const gs_bind_req* d_binds, uint32_t n, const u64* 
                              gs_pod_record* d_pods, uint32_t max_pods, const uint32_t* d_nodeinfo, uint32_t n_nodes,
                              const u64* d_cap, uint32_t dev_stride, u64* d_used, int32_t* d_out_dev, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    k_bind_scan<<<(n + 127) / 128, 128, 0, st>>>(d_binds, n, d_sorted_nodes, d_perm, d_pods, max_pods, d_nodeinfo,
-                                                 n_nodes, d_cap, dev_stride, d_used, d_out_dev);
+    if (dev_stride == 8)
+        k_bind_scan<true><<<(n + 127) / 128, 128, 0, st>>>(d_binds, n, d_sorted_nodes, d_perm, d_pods, max_pods,
+                                                           d_nodeinfo, n_nodes, d_cap, dev_stride, d_used, d_out_dev);
+    else
+        k_bind_scan<false><<<(n + 127) / 128, 128, 0, st>>>(d_binds, n, d_sorted_nodes, d_perm, d_pods, max_pods,
+                                                            d_nodeinfo, n_nodes, d_cap, dev_stride, d_used, d_out_dev);
     return cudaGetLastError();
 }
 

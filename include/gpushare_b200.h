@@ -62,7 +62,7 @@ enum {
 /* Most devices a node may have (len(NodeInfo.devs), pkg/cache/nodeinfo.go:32-35). */
 #define GS_MAX_DEVS 64
 /* Rows one filter / bind launch handles; larger batches are split internally. */
-#define GS_MAX_BATCH 16384
+#define GS_MAX_BATCH 12288
 
 /* One node as NewNodeInfo freezes it (pkg/cache/nodeinfo.go:29-45). */
 typedef struct gs_node {
@@ -169,6 +169,15 @@ int gs_filter_batch(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint32
  * ordered by the caller (they share the snapshot's work buffers). */
 int gs_filter_batch_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods,
                            uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream);
+/* Profiling aid: launches only the K3 stages named in stage_mask (GS_STAGE_*), in order, on the
+ * same buffers gs_filter_batch_device uses (n_pods <= GS_MAX_BATCH).  Later stages read what earlier
+ * stages left in the snapshot's work buffers, so run the full set once first.  bench.py times each
+ * stage with CUDA events around a loop of such calls. */
+#define GS_STAGE_SORT 1u
+#define GS_STAGE_NODE_RANK 2u
+#define GS_STAGE_EXPAND 4u
+int gs_filter_stages_device(gs_snapshot* s, uint32_t stage_mask, const uint64_t* d_req, uint32_t n_pods,
+                            uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream);
 /* Per-node class bytes (GS_NODE_*) for rendering FailedNodes. */
 int gs_node_classes(gs_snapshot* s, uint8_t* out_class, uint32_t n);
 
