@@ -14,6 +14,9 @@
 //                   nodes into a word with 10 LOP3s; only nodes whose bucket lies inside the tile's own
 //                   bucket range need the exact 64-bit comparison.
 // (k_radix_sort, a stable single-CTA LSD radix sort, orders the bind queue by node for K4.)
+#include <stdio.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -346,71 +349,135 @@ k_group_pods(const u64* __restrict__ req, uint32_t n_pods, FilterBuffers fb) {
 __device__ __forceinline__ uint32_t planes_ge(const uint32_t (&a)[kRankPlanes], uint32_t t) {
     uint32_t ge = 0xffffffffu;
 #pragma unroll
-    for (int k = 0; k < kRankPlanes; ++k) {
-        const uint32_t m = 0u - ((t >> k) & 1u);
-        ge = (m & a[k] & ge) | (~m & (a[k] | ge));
-    }
+    for (int k = 0; k < kRankPlanes; ++k) ge = ((t >> k) & 1u) ? (a[k] & ge) : (a[k] | ge);  // t is warp-uniform
     return ge;
 }
 
 // A tile is kTileRows consecutive grouped pods x kTileWords words (4096 nodes); its rows span request
 // buckets [bmin, bmax].  A node with q' > bmax passes in every row (base word), one with q' < bmin in
 // none; only nodes with bmin <= q' <= bmax need the exact 64-bit comparison key >= req per row.  Words
-// holding such nodes are recomputed row by row into a small shared-memory patch (a few such nodes:
-// lane = row, keys in registers; many: lane = node, one ballot per row); every other word goes from
-// registers straight to global memory.  Stores are 16 bytes per lane, 512 contiguous bytes per warp.
-constexpr uint32_t kPatchWords = 3072;  // patch capacity in 32-bit words (rows x patched words per sub-pass)
+// holding such nodes are recomputed row by row (a few such nodes: lane = row, exact compares; many:
+// lane = node, a binary search over the tile's sorted requests) into a small shared-memory patch;
+// every other word goes from registers straight to global memory.  Stores are 16 bytes per lane, 512
+// contiguous bytes per warp and row.  (Bulk asynchronous stores of 512-byte row segments from a
+// shared-memory tile were measured slower than this: profiles/NOTES.md.)
 constexpr int kSparseMax = 4;           // up to this many compared nodes a word takes the lane = row path
-constexpr int kDenseRows = 8;           // rows per unrolled step of the lane = node path
+constexpr uint32_t kPatchWords = 4096;  // patch capacity in 32-bit words (rows x patched words per sub-pass)
 
 struct ExpandSmem {
-    uint32_t patch[kPatchWords];
-    u64 req[kTileRows + kDenseRows];    // requests of the tile's rows (+ padding read by the unrolled loop)
+    uint32_t patch[kPatchWords];        // per-row values of the words that differ from row to row
+    u64 req[kTileRows];                 // requests of the tile's rows (~0 beyond the last row)
+    u64 req_sorted[kTileRows];          // the same in ascending order (only when a dense word needs it)
     u64 ekey[kTileWords * kSparseMax];  // keys of the compared nodes of sparse words
+    u64 off_sorted[kTileRows];
     uint32_t ebits[kTileWords];         // their bit positions, 8 bits each (0xff = unused)
     uint32_t basew[kTileWords];         // nodes passing in every row
     uint32_t somew[kTileWords];         // nodes that can pass in some row (q' >= bmin)
-    uint32_t row_of[kTileRows];         // output row (pod index) of every tile row
-    uint8_t plist[kTileWords];          // words to patch
-    uint8_t pidx[kTileWords];           // position in plist, 0xff = not patched
-    uint32_t n_partial, tile;
+    u64 row_off[kTileRows];             // word offset of every tile row's output row (pod index x row stride)
+    uint8_t plist[kTileWords];          // words that need per-row values
+    uint8_t pidx[kTileWords];           // position in plist, 0xff = the word is the same in every row
+    uint32_t n_partial, any_dense;
 };
 
+// Inputs of one tile, brought in by bulk asynchronous copies (TMA) that complete on an mbarrier.  They
+// are requested kPrefetch tiles ahead: ordinary loads issued from a CTA that is streaming stores queue
+// up behind those stores and would stall every tile for microseconds.
+constexpr int kPrefetch = 3;
+struct __align__(128) TileInputs {
+    uint32_t planes[kRankPlanes * kTileWords];  // bucket-id planes of the tile's 128 words
+    u64 req[kTileRows];                         // requests of the tile's rows
+    uint16_t perm[kTileRows];                   // their pod indices
+    uint16_t bucket[kTileRows];                 // their 1-based buckets
+};
+constexpr uint32_t kTileInputBytes = sizeof(TileInputs);
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(sdst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
 template <bool kVec>
-__global__ void __launch_bounds__(kExpandThreads)
+__global__ void __launch_bounds__(kExpandThreads, 5)
 k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_stride, uint32_t* __restrict__ out,
-         uint32_t n_col_blocks, uint32_t n_tiles) {
-    __shared__ __align__(16) ExpandSmem sm;
+         uint32_t n_col_blocks, uint32_t inv_col_blocks, uint32_t n_tiles) {
+    __shared__ __align__(128) ExpandSmem sm;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr uint32_t kWarps = kExpandThreads / 32;
     static_assert(kExpandThreads >= kTileWords + kTileRows, "phase A: one thread per word, one per row");
     const uint32_t* __restrict__ planes = fb.planes;
     const u64* __restrict__ node_key = fb.node_key;
 
-    // dynamic tile scheduler; the ticket for the next tile is taken while the current one is processed
-    uint32_t ticket = 0;
-    if (tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);
-    for (;;) {
-        if (tid == 0) {
-            sm.tile = ticket;
-            sm.n_partial = 0;
-        }
-        __syncthreads();
-        if (sm.tile >= n_tiles) break;
-        if (tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);
-        const uint32_t tile = n_tiles - 1u - sm.tile;  // high buckets first: that is where node keys cluster
-        const uint32_t rt = tile / n_col_blocks, cb = tile - rt * n_col_blocks;
+    __shared__ TileInputs tin[kPrefetch];
+    __shared__ __align__(8) uint64_t tin_bar[kPrefetch];
+
+    // thread 0: request the inputs of the tile with ticket `ticket_no` into stage `stage`
+    auto request = [&](uint32_t ticket_no, uint32_t stage) {
+        if (ticket_no >= n_tiles) return;
+        const uint32_t t = n_tiles - 1u - ticket_no;  // high buckets first: that is where node keys cluster
+        const uint32_t rt = inv_col_blocks ? __umulhi(t, inv_col_blocks) : t, cb = t - rt * n_col_blocks;  // t / n_col_blocks
+        const uint32_t j0 = rt * kTileRows;
+        TileInputs& in = tin[stage];
+        mbar_expect_tx(&tin_bar[stage], kTileInputBytes);
+        bulk_load(in.planes, planes + (size_t)cb * kRankPlanes * kTileWords, sizeof(in.planes), &tin_bar[stage]);
+        bulk_load(in.req, fb.grouped_req + j0, sizeof(in.req), &tin_bar[stage]);
+        bulk_load(in.perm, fb.perm + j0, sizeof(in.perm), &tin_bar[stage]);
+        bulk_load(in.bucket, fb.row_bucket + j0, sizeof(in.bucket), &tin_bar[stage]);
+    };
+
+    // Static round-robin tile schedule: tile numbers blockIdx.x + it * gridDim.x.  (A dynamic ticket
+    // scheduler with look-ahead hoards tickets when there are only ~3 tiles per CTA: profiles/NOTES.md.)
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < kPrefetch; ++i) mbar_init(&tin_bar[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        sm.n_partial = 0;
+        sm.any_dense = 0;
+#pragma unroll
+        for (int i = 0; i < kPrefetch; ++i) request(blockIdx.x + i * gridDim.x, i);
+    }
+    __syncthreads();
+    uint32_t cur = blockIdx.x;
+
+    for (uint32_t it = 0; cur < n_tiles; ++it) {
+        const uint32_t stage = it % kPrefetch, parity = (it / kPrefetch) & 1u;
+        const uint32_t tile = n_tiles - 1u - cur;
+        const uint32_t rt = inv_col_blocks ? __umulhi(tile, inv_col_blocks) : tile, cb = tile - rt * n_col_blocks;
         const uint32_t j0 = rt * kTileRows;
         const uint32_t rows = min((uint32_t)kTileRows, n_pods - j0);
         const uint32_t w0 = cb * kTileWords;
+        const TileInputs& in = tin[stage];
+        unsigned long long* dbg = (fb.dbg && tid == 0 && it < 4) ? fb.dbg + ((size_t)blockIdx.x * 4 + it) * 8 : nullptr;
+        if (dbg) { unsigned long long g; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g)); dbg[0] = g; dbg[1] = clock64(); }
+        mbar_wait(&tin_bar[stage], parity);
 
         // A: one thread per word (threads 0..127), one per row (threads 128..191)
         if (tid < kTileWords) {
             uint32_t a[kRankPlanes];
-            const uint32_t* src = planes + (size_t)cb * kRankPlanes * kTileWords + tid;
 #pragma unroll
-            for (int k = 0; k < kRankPlanes; ++k) a[k] = __ldg(src + k * kTileWords);
-            const uint32_t bmin = fb.row_bucket[j0], bmax = fb.row_bucket[j0 + rows - 1];
+            for (int k = 0; k < kRankPlanes; ++k) a[k] = in.planes[k * kTileWords + tid];
+            const uint32_t bmin = in.bucket[0], bmax = in.bucket[rows - 1];
             // the last bucket is open-ended: no node is known to cover all of it
             const uint32_t t_all = bmax == kBuckets ? kBuckets + 2u : bmax + 1u;
             const uint32_t all_rows = planes_ge(a, t_all);
@@ -439,31 +506,51 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
 #pragma unroll
                     for (int i = 0; i < kSparseMax; ++i) sm.ekey[tid * kSparseMax + i] = kk[i];
                     sm.ebits[tid] = eb;
+                } else {
+                    sm.any_dense = 1;
                 }
             }
             sm.pidx[tid] = pi;
         } else if (tid < kTileWords + kTileRows) {
             const uint32_t r = tid - kTileWords;
-            if (r < rows) {
-                sm.row_of[r] = (uint32_t)fb.perm[j0 + r];
-                sm.req[r] = fb.grouped_req[j0 + r];
-            } else {
-                sm.req[r] = ~0ull;
-            }
-        } else if (tid < kTileWords + kTileRows + kDenseRows) {
-            sm.req[tid - kTileWords] = ~0ull;
+            const uint32_t row = (fb.debug_identity & 1u) ? j0 + r : (uint32_t)in.perm[r];
+            sm.row_off[r] = (u64)row * row_stride;
+            sm.req[r] = r < rows ? in.req[r] : ~0ull;
         }
-        __syncthreads();
+        if (dbg) dbg[2] = clock64();
+        __syncthreads();  // phase A results are visible; nobody reads this stage's inputs any more
+        if (dbg) dbg[3] = clock64();
 
+        const uint32_t nxt = cur + gridDim.x;
         const uint32_t np = sm.n_partial;
+        const bool dense = sm.any_dense != 0;
+        if (tid == 0) request(cur + kPrefetch * gridDim.x, stage);  // refill the stage just consumed
+
+        // Words with many compared nodes want the tile's rows in ascending request order: then a node's
+        // column is a prefix of ones and one binary search per node replaces a comparison per row.
+        if (dense && tid < kTileRows) {
+            const u64 mine = sm.req[tid];
+            uint32_t rank = 0;
+#pragma unroll 8
+            for (uint32_t o = 0; o < kTileRows; ++o) {
+                const u64 other = sm.req[o];
+                rank += (other < mine || (other == mine && o < tid)) ? 1u : 0u;
+            }
+            sm.req_sorted[rank] = mine;
+            sm.off_sorted[rank] = sm.row_off[tid];
+        }
+        const u64* __restrict__ treq = dense ? sm.req_sorted : sm.req;
+        const u64* __restrict__ toff = dense ? sm.off_sorted : sm.row_off;
+        if (dbg) dbg[4] = clock64();
         // rows per sub-pass so that np patched words x rows fit the patch (odd stride spreads banks)
         uint32_t pstride = np ? kPatchWords / np : kPatchWords;
         pstride -= (pstride & 1u) ^ 1u;
         const uint32_t sub_rows = min((uint32_t)kTileRows, pstride);
         for (uint32_t r0 = 0; r0 < rows; r0 += sub_rows) {
             const uint32_t rcount = min(sub_rows, rows - r0);
-            // C: patched words
             if (np) {
+                __syncthreads();
+                // C: words that differ from row to row
                 u64 nextkey = 0;
                 {
                     const uint32_t t = warp < np ? sm.plist[warp] : 0u;
@@ -488,7 +575,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             kb[i] = bit == 0xffu ? 0u : 1u << bit;
                         }
                         for (uint32_t rr = lane; rr < rcount; rr += 32) {
-                            const u64 rq = sm.req[r0 + rr];
+                            const u64 rq = treq[r0 + rr];
                             uint32_t v = base;
 #pragma unroll
                             for (int i = 0; i < kSparseMax; ++i)
@@ -496,24 +583,43 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             prow[rr] = v;
                         }
                     } else {
-                        // lane = node; one ballot per row, kDenseRows rows per step.  Masking with `some`
-                        // clears the nodes that can never pass (q' == 0 stores key 0, which would match
-                        // a zero request).
-                        for (uint32_t g = 0; g < rcount; g += kDenseRows) {
-                            uint32_t mine = 0;
+                        // lane = node.  Rows are in ascending request order, so the node passes in exactly
+                        // the first cnt rows, cnt = #{rows : req <= key}.  Nodes outside `some` never pass
+                        // (q' == 0 stores key 0, which would match a zero request).
+                        uint32_t cnt = 0;
+                        if ((some >> lane) & 1u) {
+                            uint32_t lo = 0, hi = rows;
 #pragma unroll
-                            for (int i = 0; i < kDenseRows; ++i) {
-                                const u64 rq = sm.req[r0 + g + i];
-                                const uint32_t bal = __ballot_sync(0xffffffffu, mykey >= rq) & some;
-                                if ((int)lane == i) mine = bal;
+                            for (int it = 0; it < 7; ++it) {  // rows <= 64
+                                if (lo < hi) {
+                                    const uint32_t mid = (lo + hi) >> 1;
+                                    if (treq[mid] <= mykey)
+                                        lo = mid + 1;
+                                    else
+                                        hi = mid;
+                                }
                             }
-                            if (lane < kDenseRows && g + lane < rcount) prow[g + lane] = mine;
+                            cnt = lo;
+                        }
+                        uint32_t pl[7];  // cnt (0..64) bit-sliced over the word's 32 nodes
+#pragma unroll
+                        for (int q = 0; q < 7; ++q) pl[q] = __ballot_sync(0xffffffffu, (cnt >> q) & 1u);
+                        for (uint32_t rr = lane; rr < rcount; rr += 32) {
+                            const uint32_t thr = r0 + rr + 1;  // bit set iff cnt >= row + 1
+                            uint32_t ge = 0xffffffffu;
+#pragma unroll
+                            for (int q = 0; q < 7; ++q) {
+                                const uint32_t m = 0u - ((thr >> q) & 1u);
+                                ge = (m & pl[q] & ge) | (~m & (pl[q] | ge));
+                            }
+                            prow[rr] = ge;
                         }
                     }
                 }
                 __syncthreads();
             }
-            // D: lane owns 4 words, warp owns rows r0 + warp, r0 + warp + kWarps, ...
+            // D: lane owns 4 words, warp owns rows r0 + warp, r0 + warp + kWarps, ...; 16 bytes per
+            // lane, 512 contiguous bytes per warp and row
             if (kVec) {
                 const uint32_t wcol = w0 + lane * 4;
                 if (wcol < words_out) {
@@ -521,8 +627,9 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     const uint32_t p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lane * 4]);
                     uint32_t* dst = out + wcol;
                     if (p4 == 0xffffffffu) {
+#pragma unroll 4
                         for (uint32_t rr = warp; rr < rcount; rr += kWarps)
-                            __stcs(reinterpret_cast<uint4*>(dst + (size_t)sm.row_of[r0 + rr] * row_stride), b4);
+                            __stcs(reinterpret_cast<uint4*>(dst + toff[r0 + rr]), b4);
                     } else {
                         const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
                         for (uint32_t rr = warp; rr < rcount; rr += kWarps) {
@@ -531,13 +638,13 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             if (k1 != 0xffu) v.y = sm.patch[k1 * pstride + rr];
                             if (k2 != 0xffu) v.z = sm.patch[k2 * pstride + rr];
                             if (k3 != 0xffu) v.w = sm.patch[k3 * pstride + rr];
-                            __stcs(reinterpret_cast<uint4*>(dst + (size_t)sm.row_of[r0 + rr] * row_stride), v);
+                            __stcs(reinterpret_cast<uint4*>(dst + toff[r0 + rr]), v);
                         }
                     }
                 }
             } else {
                 for (uint32_t rr = warp; rr < rcount; rr += kWarps) {
-                    uint32_t* dst = out + (size_t)sm.row_of[r0 + rr] * row_stride + w0;
+                    uint32_t* dst = out + toff[r0 + rr] + w0;
 #pragma unroll
                     for (int c = 0; c < kTileWords / 32; ++c) {
                         const uint32_t wl = c * 32 + lane;
@@ -548,16 +655,15 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     }
                 }
             }
-            if (np && r0 + sub_rows < rows) __syncthreads();  // the next sub-pass overwrites the patch
         }
-    }
-    // the last CTA out re-arms the scheduler for the next launch
-    if (tid == 0) {
-        __threadfence();
-        if (atomicAdd(&fb.sched[1], 1u) == gridDim.x - 1) {
-            fb.sched[0] = 0;
-            fb.sched[1] = 0;
+        if (tid == 0) {  // everyone copied these to registers before the barriers above (or they are 0)
+            sm.n_partial = 0;
+            sm.any_dense = 0;
         }
+        if (dbg) dbg[5] = clock64();
+        __syncthreads();  // phase A of the next tile rewrites what phase D was reading
+        if (dbg) { unsigned long long g; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g)); dbg[6] = clock64(); dbg[7] = g; }
+        cur = nxt;
     }
 }
 
@@ -570,6 +676,11 @@ static cudaError_t ensure_attrs(int device) {
     if (device >= 0 && device < 64 && g_attr_done[device]) return cudaSuccess;
     cudaError_t e = cudaFuncSetAttribute(k_radix_sort<BindKeyLoader>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)kSortSmemBytes);
+    if (e != cudaSuccess) return e;
+    // k_expand wants as many resident CTAs as its shared memory allows: ask for the largest carve-out
+    e = cudaFuncSetAttribute(k_expand<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_expand<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
     if (device >= 0 && device < 64) g_attr_done[device] = true;
     return cudaSuccess;
@@ -605,18 +716,51 @@ cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
                           uint32_t row_stride, uint32_t* d_out, cudaStream_t st) {
     if (n_pods == 0 || words == 0) return cudaSuccess;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaError_t ea = ensure_attrs(dev);
+        if (ea != cudaSuccess) return ea;
+    }
     const bool vec = (row_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_out) & 15u) == 0);
     const uint32_t words_out = vec ? ((words + 3u) & ~3u) : words;
     const uint32_t n_col_blocks = (words_out + kTileWords - 1) / kTileWords;
     const uint32_t n_row_tiles = (n_pods + kTileRows - 1) / kTileRows;
     const uint32_t n_tiles = n_col_blocks * n_row_tiles;
-    const uint32_t per_sm = 6;  // resident CTAs per SM (256 threads, ~20 KB shared each)
+    const uint32_t per_sm = 5;  // resident CTAs per SM (256 threads, 48 registers, 42 KB shared)
     uint32_t grid = (uint32_t)sm_count * per_sm;
     if (grid > n_tiles) grid = n_tiles;
+    // static schedule: the smallest grid that gives the same number of rounds, so all CTAs get the same share
+    const uint32_t rounds = (n_tiles + grid - 1) / grid;
+    grid = (n_tiles + rounds - 1) / rounds;
+    // exact t / n_col_blocks as a multiply-high for every t below 2^32 / n_col_blocks (n_tiles is far
+    // smaller); 0 stands for "one column block" (2^32 does not fit)
+    const uint32_t inv = n_col_blocks == 1 ? 0u : (uint32_t)((0x100000000ull + n_col_blocks - 1) / n_col_blocks);
+    FilterBuffers fbd = fb;
+    fbd.debug_identity = getenv("GS_DEBUG_IDENTITY_PERM") ? 1u : 0u;
+    if (getenv("GS_DEBUG_GRID")) grid = (uint32_t)atoi(getenv("GS_DEBUG_GRID"));
+    static unsigned long long* d_dbg = nullptr;
+    const char* dbg_path = getenv("GS_DEBUG_TIMES");
+    if (dbg_path) {
+        if (!d_dbg) cudaMalloc(&d_dbg, (size_t)4096 * 4 * 8 * 8);
+        cudaMemsetAsync(d_dbg, 0, (size_t)4096 * 4 * 8 * 8, st);
+        fbd.dbg = d_dbg;
+    }
     if (vec)
-        k_expand<true><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, n_tiles);
+        k_expand<true><<<grid, kExpandThreads, 0, st>>>(fbd, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
     else
-        k_expand<false><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, n_tiles);
+        k_expand<false><<<grid, kExpandThreads, 0, st>>>(fbd, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
+    if (dbg_path) {
+        cudaStreamSynchronize(st);
+        static unsigned long long h[4096 * 4 * 8];
+        cudaMemcpy(h, d_dbg, sizeof h, cudaMemcpyDeviceToHost);
+        FILE* f = fopen(dbg_path, "wb");
+        if (f) {
+            fwrite(&grid, 4, 1, f);
+            fwrite(h, 8, (size_t)grid * 32, f);
+            fclose(f);
+        }
+    }
     return cudaGetLastError();
 }
 

@@ -1,0 +1,136 @@
+// Development aid: write bandwidth when a 62.7 MB buffer is written as chunks of S bytes whose order
+// over the grid is either sequential or "tile-like" (64 rows of a column block, row pitch 6272 B).
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+__global__ void k_seq(uint4* out, size_t n16) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i < n16; i += (size_t)gridDim.x * blockDim.x) out[i] = make_uint4(1, 2, 3, 4);
+}
+// tile-like: tile t -> (row tile rt, col block cb); warp w writes rows w, w+8, ...; lane 16 B
+__global__ void k_tile(uint4* out, int n_rows, int pitch16, int cb_count, int seg16, int tile_rows) {
+    int n_tiles = (n_rows / tile_rows) * cb_count;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        int rt = t / cb_count, cb = t % cb_count;
+        for (int r = warp; r < tile_rows; r += nw)
+            for (int c = lane; c < seg16; c += 32) {
+                int col = cb * seg16 + c;
+                if (col < pitch16) out[(size_t)(rt * tile_rows + r) * pitch16 + col] = make_uint4(1, 2, 3, 4);
+            }
+    }
+}
+template <int MODE>  // 0 = st.global.cs from registers, 1 = smem tile + TMA bulk store, 2 = as 1 but wait before reuse only
+__global__ void k_tile2(uint4* out, int n_rows, int pitch16, int cb_count, int seg16, int tile_rows) {
+    extern __shared__ __align__(128) uint4 sbuf[];
+    int n_tiles = (n_rows / tile_rows) * cb_count;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        int rt = t / cb_count, cb = t % cb_count;
+        if (MODE == 0) {
+            for (int r = warp; r < tile_rows; r += nw)
+                for (int c = lane; c < seg16; c += 32) {
+                    int col = cb * seg16 + c;
+                    if (col < pitch16) __stcs(&out[(size_t)(rt * tile_rows + r) * pitch16 + col], make_uint4(1, 2, 3, 4));
+                }
+        } else {
+            if (warp == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncthreads();
+            for (int r = warp; r < tile_rows; r += nw)
+                for (int c = lane; c < seg16; c += 32) sbuf[r * (seg16 + 1) + c] = make_uint4(1, 2, 3, 4);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (warp == 0) {
+                int segb = min(seg16, pitch16 - cb * seg16) * 16;
+                for (int r = lane; r < tile_rows; r += 32) {
+                    void* g = &out[(size_t)(rt * tile_rows + r) * pitch16 + cb * seg16];
+                    unsigned sa = (unsigned)__cvta_generic_to_shared(&sbuf[r * (seg16 + 1)]);
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g), "r"(sa), "r"(segb) : "memory");
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+    }
+    if (MODE != 0 && warp == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+// MODE bits: 1 = __syncthreads twice per tile, 2 = dynamic atomic tile scheduler, 4 = per-tile global loads
+// feeding the stored value, 8 = row offsets read from shared memory, 16 = 100 dependent ALU ops per tile
+template <int MODE>
+__global__ void k_tile3(uint4* out, int n_rows, int pitch16, int cb_count, int seg16, int tile_rows,
+                        unsigned* sched, const unsigned* __restrict__ aux) {
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_off[64];
+    int n_tiles = (n_rows / tile_rows) * cb_count;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    int t = blockIdx.x;
+    for (;;) {
+        if (MODE & 2) {
+            if (threadIdx.x == 0) s_tile = atomicAdd(&sched[0], 1u);
+            __syncthreads();
+            t = s_tile;
+        }
+        if (t >= n_tiles) break;
+        int rt = t / cb_count, cb = t % cb_count;
+        unsigned x = 1;
+        if (MODE & 4) x = aux[(t * 131 + threadIdx.x) & 0xffff];
+        if (MODE & 16) {
+#pragma unroll 1
+            for (int i = 0; i < 100; ++i) x = x * 1664525u + 1013904223u;
+        }
+        if (MODE & 8) {
+            if (threadIdx.x < tile_rows) s_off[threadIdx.x] = (unsigned long long)(rt * tile_rows + threadIdx.x) * pitch16;
+        }
+        if (MODE & 1) __syncthreads();
+        for (int r = warp; r < tile_rows; r += nw)
+            for (int c = lane; c < seg16; c += 32) {
+                int col = cb * seg16 + c;
+                size_t off = (MODE & 8) ? s_off[r] : (size_t)(rt * tile_rows + r) * pitch16;
+                if (col < pitch16) __stcs(&out[off + col], make_uint4(x, 2, 3, 4));
+            }
+        if (MODE & 1) __syncthreads();
+        if (!(MODE & 2)) { t += gridDim.x; }
+    }
+    if ((MODE & 2) && threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&sched[1], 1u) == gridDim.x - 1) { sched[0] = 0; sched[1] = 0; }
+    }
+}
+int main() {
+    const int rows = 9984, pitch = 6272;  // bytes
+    size_t bytes = (size_t)rows * pitch;
+    uint4* buf[4];
+    for (auto& b : buf) cudaMalloc(&b, bytes);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    auto run = [&](const char* name, auto launch) {
+        for (int i = 0; i < 5; ++i) launch(buf[i % 4]);
+        cudaEventRecord(e0);
+        for (int i = 0; i < 50; ++i) launch(buf[i % 4]);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        printf("%-40s %7.1f us  %7.1f GB/s  (%s)\n", name, ms / 50 * 1e3, bytes / (ms / 50 * 1e-3) / 1e9, cudaGetErrorString(cudaGetLastError()));
+    };
+    run("sequential grid-stride 148x8x256", [&](uint4* o) { k_seq<<<148 * 8, 256>>>(o, bytes / 16); });
+    run("sequential one-shot", [&](uint4* o) { k_seq<<<(unsigned)(bytes / 16 / 256), 256>>>(o, bytes / 16); });
+    int segs[] = {8, 32, 98, 392};  // 16-byte units: 128 B, 512 B, 1568 B, 6272 B
+    int trs[] = {64, 16, 8};
+    for (int tr : trs)
+        for (int s : segs) {
+            int cbc = (392 + s - 1) / s;
+            char name[96];
+            snprintf(name, sizeof name, "tile %d rows x %d B, grid 740", tr, s * 16);
+            run(name, [&](uint4* o) { k_tile<<<740, 256>>>(o, rows, 392, cbc, s, tr); });
+        }
+    for (int grid : {740, 1480}) {
+        char name[96];
+        snprintf(name, sizeof name, "st.cs regs 64 x 512 B, grid %d", grid);
+        run(name, [&](uint4* o) { k_tile2<0><<<grid, 256>>>(o, rows, 392, 13, 32, 64); });
+        snprintf(name, sizeof name, "smem+TMA bulk 64 x 512 B, grid %d", grid);
+        cudaFuncSetAttribute(k_tile2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 33 * 16);
+        run(name, [&](uint4* o) { k_tile2<1><<<grid, 256, 64 * 33 * 16>>>(o, rows, 392, 13, 32, 64); });
+    }
+    unsigned* sched; cudaMalloc(&sched, 8); cudaMemset(sched, 0, 8);
+    unsigned* aux; cudaMalloc(&aux, 65536 * 4); cudaMemset(aux, 1, 65536 * 4);
+#define RUN3(M) run("k_tile3 mode " #M, [&](uint4* o) { k_tile3<M><<<740, 256>>>(o, rows, 392, 13, 32, 64, sched, aux); });
+    RUN3(1) RUN3(9) RUN3(17) RUN3(25) RUN3(29) RUN3(31)
+    return 0;
+}
