@@ -150,8 +150,6 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     fb.planes = s->d_rank_planes;
     fb.node_key = s->d_node_key;
     fb.sched = s->d_sched;
-    fb.debug_identity = 0;
-    fb.dbg = nullptr;
     // bucket scale: requests up to the largest device capacity spread over all 512 buckets
     uint32_t bits = 0;
     while (bits < 64 && (s->max_capacity >> bits) != 0) ++bits;

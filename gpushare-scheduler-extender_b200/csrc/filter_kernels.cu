@@ -14,9 +14,6 @@
 //                   nodes into a word with 10 LOP3s; only nodes whose bucket lies inside the tile's own
 //                   bucket range need the exact 64-bit comparison.
 // (k_radix_sort, a stable single-CTA LSD radix sort, orders the bind queue by node for K4.)
-#include <stdio.h>
-#include <stdlib.h>
-
 #include "common.cuh"
 #include "kernels.h"
 
@@ -374,15 +371,17 @@ struct ExpandSmem {
     uint32_t basew[kTileWords];         // nodes passing in every row
     uint32_t somew[kTileWords];         // nodes that can pass in some row (q' >= bmin)
     u64 row_off[kTileRows];             // word offset of every tile row's output row (pod index x row stride)
+    uint32_t cntp[kTileWords * 8];      // dense words: per-node pass counts (0..64), bit-sliced, 7 planes used
     uint8_t plist[kTileWords];          // words that need per-row values
     uint8_t pidx[kTileWords];           // position in plist, 0xff = the word is the same in every row
-    uint32_t n_partial, any_dense;
+    uint8_t dlist[kTileWords];          // the dense ones among them
+    uint32_t n_partial, n_dense;
 };
 
 // Inputs of one tile, brought in by bulk asynchronous copies (TMA) that complete on an mbarrier.  They
 // are requested kPrefetch tiles ahead: ordinary loads issued from a CTA that is streaming stores queue
 // up behind those stores and would stall every tile for microseconds.
-constexpr int kPrefetch = 3;
+constexpr int kPrefetch = 2;
 struct __align__(128) TileInputs {
     uint32_t planes[kRankPlanes * kTileWords];  // bucket-id planes of the tile's 128 words
     u64 req[kTileRows];                         // requests of the tile's rows
@@ -431,6 +430,8 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
 
     __shared__ TileInputs tin[kPrefetch];
     __shared__ __align__(8) uint64_t tin_bar[kPrefetch];
+    __shared__ __align__(8) uint64_t key_bar;  // completion of on-demand key loads for dense words
+    uint32_t key_phase = 0;
 
     // thread 0: request the inputs of the tile with ticket `ticket_no` into stage `stage`
     auto request = [&](uint32_t ticket_no, uint32_t stage) {
@@ -452,8 +453,10 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
 #pragma unroll
         for (int i = 0; i < kPrefetch; ++i) mbar_init(&tin_bar[i], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_init(&key_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         sm.n_partial = 0;
-        sm.any_dense = 0;
+        sm.n_dense = 0;
 #pragma unroll
         for (int i = 0; i < kPrefetch; ++i) request(blockIdx.x + i * gridDim.x, i);
     }
@@ -468,8 +471,6 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         const uint32_t rows = min((uint32_t)kTileRows, n_pods - j0);
         const uint32_t w0 = cb * kTileWords;
         const TileInputs& in = tin[stage];
-        unsigned long long* dbg = (fb.dbg && tid == 0 && it < 4) ? fb.dbg + ((size_t)blockIdx.x * 4 + it) * 8 : nullptr;
-        if (dbg) { unsigned long long g; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g)); dbg[0] = g; dbg[1] = clock64(); }
         mbar_wait(&tin_bar[stage], parity);
 
         // A: one thread per word (threads 0..127), one per row (threads 128..191)
@@ -485,11 +486,11 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             sm.basew[tid] = all_rows;
             sm.somew[tid] = some_rows;
             uint32_t pm = some_rows & ~all_rows;
-            uint8_t pi = 0xff;
+            uint8_t pi = 0xff;  // 0xff: same word in every row, 0xfe: dense, else: index into the patch
             if (pm) {
-                pi = (uint8_t)atomicAdd(&sm.n_partial, 1u);
-                sm.plist[pi] = (uint8_t)tid;
                 if (__popc(pm) <= kSparseMax) {
+                    pi = (uint8_t)atomicAdd(&sm.n_partial, 1u);
+                    sm.plist[pi] = (uint8_t)tid;
                     const u64* keys = node_key + (size_t)(w0 + tid) * 32;
                     uint32_t eb = 0xffffffffu;
                     u64 kk[kSparseMax];
@@ -507,27 +508,36 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     for (int i = 0; i < kSparseMax; ++i) sm.ekey[tid * kSparseMax + i] = kk[i];
                     sm.ebits[tid] = eb;
                 } else {
-                    sm.any_dense = 1;
+                    pi = 0xfe;
+                    sm.dlist[atomicAdd(&sm.n_dense, 1u)] = (uint8_t)tid;
                 }
             }
             sm.pidx[tid] = pi;
         } else if (tid < kTileWords + kTileRows) {
             const uint32_t r = tid - kTileWords;
-            const uint32_t row = (fb.debug_identity & 1u) ? j0 + r : (uint32_t)in.perm[r];
+            const uint32_t row = (uint32_t)in.perm[r];
             sm.row_off[r] = (u64)row * row_stride;
             sm.req[r] = r < rows ? in.req[r] : ~0ull;
         }
-        if (dbg) dbg[2] = clock64();
         __syncthreads();  // phase A results are visible; nobody reads this stage's inputs any more
-        if (dbg) dbg[3] = clock64();
 
         const uint32_t nxt = cur + gridDim.x;
         const uint32_t np = sm.n_partial;
-        const bool dense = sm.any_dense != 0;
+        const uint32_t nd = sm.n_dense;
+        const bool dense = nd != 0;
         if (tid == 0) request(cur + kPrefetch * gridDim.x, stage);  // refill the stage just consumed
 
         // Words with many compared nodes want the tile's rows in ascending request order: then a node's
         // column is a prefix of ones and one binary search per node replaces a comparison per row.
+        u64* kstage = reinterpret_cast<u64*>(sm.patch);
+        // one bulk copy brings the keys of 64 consecutive words (16 KB) into the staging area
+        auto fetch_keys = [&](uint32_t half) {
+            if (tid == 0) {
+                mbar_expect_tx(&key_bar, 64u * 256u);
+                bulk_load(kstage, node_key + (size_t)(w0 + half * 64u) * 32, 64u * 256u, &key_bar);
+            }
+        };
+        if (dense) fetch_keys(0);  // overlaps the sort below
         if (dense && tid < kTileRows) {
             const u64 mine = sm.req[tid];
             uint32_t rank = 0;
@@ -541,7 +551,39 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         }
         const u64* __restrict__ treq = dense ? sm.req_sorted : sm.req;
         const u64* __restrict__ toff = dense ? sm.off_sorted : sm.row_off;
-        if (dbg) dbg[4] = clock64();
+        if (dense) {
+            // Dense words: the node keys of the tile arrive by bulk copy, 64 words (16 KB) at a time, staged
+            // in the patch area; per node cnt = #{rows : req <= key}; the counts are kept bit-sliced
+            // (plane-major) for phase D.
+            __syncthreads();  // req_sorted is complete
+            for (uint32_t half = 0; half < 2; ++half) {
+                if (half) fetch_keys(half);
+                mbar_wait(&key_bar, key_phase);
+                key_phase ^= 1u;
+                for (uint32_t i = warp; i < 64; i += kWarps) {
+                    const uint32_t t = half * 64 + i;
+                    if (sm.pidx[t] != 0xfeu) continue;  // warp-uniform
+                    const u64 mykey = kstage[i * 32 + lane];
+                    // cnt = #{rows : req <= key}: branch-free upper bound over the 64 sorted requests
+                    uint32_t cnt = 0;
+#pragma unroll
+                    for (uint32_t step = kTileRows / 2; step > 0; step >>= 1)
+                        if (sm.req_sorted[cnt + step - 1] <= mykey) cnt += step;
+                    if (cnt == kTileRows - 1 && sm.req_sorted[kTileRows - 1] <= mykey) cnt = kTileRows;
+                    cnt = min(cnt, rows);  // a key of ~0 also matches the padding rows
+                    // nodes outside `some` never pass (q' == 0 stores key 0, which would match a zero request)
+                    if (!((sm.somew[t] >> lane) & 1u)) cnt = 0;
+                    uint32_t mine = 0;
+#pragma unroll
+                    for (int q = 0; q < 7; ++q) {
+                        const uint32_t bal = __ballot_sync(0xffffffffu, (cnt >> q) & 1u);
+                        if ((int)lane == q) mine = bal;
+                    }
+                    if (lane < 7) sm.cntp[lane * kTileWords + t] = mine;  // plane-major
+                }
+                __syncthreads();  // the staging area is reused (second half, then the patch)
+            }
+        }
         // rows per sub-pass so that np patched words x rows fit the patch (odd stride spreads banks)
         uint32_t pstride = np ? kPatchWords / np : kPatchWords;
         pstride -= (pstride & 1u) ^ 1u;
@@ -551,69 +593,27 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             if (np) {
                 __syncthreads();
                 // C: words that differ from row to row
-                u64 nextkey = 0;
-                {
-                    const uint32_t t = warp < np ? sm.plist[warp] : 0u;
-                    nextkey = __ldg(node_key + (size_t)(w0 + t) * 32 + lane);
-                }
                 for (uint32_t k = warp; k < np; k += kWarps) {
                     const uint32_t t = sm.plist[k];
-                    const uint32_t base = sm.basew[t], some = sm.somew[t];
-                    const u64 mykey = nextkey;
-                    if (k + kWarps < np)  // prefetch the next word's keys for the lane = node path
-                        nextkey = __ldg(node_key + (size_t)(w0 + sm.plist[k + kWarps]) * 32 + lane);
+                    const uint32_t base = sm.basew[t];
                     uint32_t* prow = &sm.patch[k * pstride];
-                    if (__popc(some & ~base) <= kSparseMax) {
-                        // lane = row; the compared nodes' keys come from shared memory
-                        const uint32_t eb = sm.ebits[t];
-                        u64 kk[kSparseMax];
-                        uint32_t kb[kSparseMax];
+                    // lane = row; the compared nodes' keys come from shared memory
+                    const uint32_t eb = sm.ebits[t];
+                    u64 kk[kSparseMax];
+                    uint32_t kb[kSparseMax];
 #pragma unroll
-                        for (int i = 0; i < kSparseMax; ++i) {
-                            const uint32_t bit = (eb >> (8 * i)) & 0xffu;
-                            kk[i] = sm.ekey[t * kSparseMax + i];
-                            kb[i] = bit == 0xffu ? 0u : 1u << bit;
-                        }
-                        for (uint32_t rr = lane; rr < rcount; rr += 32) {
-                            const u64 rq = treq[r0 + rr];
-                            uint32_t v = base;
+                    for (int i = 0; i < kSparseMax; ++i) {
+                        const uint32_t bit = (eb >> (8 * i)) & 0xffu;
+                        kk[i] = sm.ekey[t * kSparseMax + i];
+                        kb[i] = bit == 0xffu ? 0u : 1u << bit;
+                    }
+                    for (uint32_t rr = lane; rr < rcount; rr += 32) {
+                        const u64 rq = treq[r0 + rr];
+                        uint32_t v = base;
 #pragma unroll
-                            for (int i = 0; i < kSparseMax; ++i)
-                                if (kk[i] >= rq) v |= kb[i];  // unused slots have kb == 0
-                            prow[rr] = v;
-                        }
-                    } else {
-                        // lane = node.  Rows are in ascending request order, so the node passes in exactly
-                        // the first cnt rows, cnt = #{rows : req <= key}.  Nodes outside `some` never pass
-                        // (q' == 0 stores key 0, which would match a zero request).
-                        uint32_t cnt = 0;
-                        if ((some >> lane) & 1u) {
-                            uint32_t lo = 0, hi = rows;
-#pragma unroll
-                            for (int it = 0; it < 7; ++it) {  // rows <= 64
-                                if (lo < hi) {
-                                    const uint32_t mid = (lo + hi) >> 1;
-                                    if (treq[mid] <= mykey)
-                                        lo = mid + 1;
-                                    else
-                                        hi = mid;
-                                }
-                            }
-                            cnt = lo;
-                        }
-                        uint32_t pl[7];  // cnt (0..64) bit-sliced over the word's 32 nodes
-#pragma unroll
-                        for (int q = 0; q < 7; ++q) pl[q] = __ballot_sync(0xffffffffu, (cnt >> q) & 1u);
-                        for (uint32_t rr = lane; rr < rcount; rr += 32) {
-                            const uint32_t thr = r0 + rr + 1;  // bit set iff cnt >= row + 1
-                            uint32_t ge = 0xffffffffu;
-#pragma unroll
-                            for (int q = 0; q < 7; ++q) {
-                                const uint32_t m = 0u - ((thr >> q) & 1u);
-                                ge = (m & pl[q] & ge) | (~m & (pl[q] | ge));
-                            }
-                            prow[rr] = ge;
-                        }
+                        for (int i = 0; i < kSparseMax; ++i)
+                            if (kk[i] >= rq) v |= kb[i];  // unused slots have kb == 0
+                        prow[rr] = v;
                     }
                 }
                 __syncthreads();
@@ -632,12 +632,31 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             __stcs(reinterpret_cast<uint4*>(dst + toff[r0 + rr]), b4);
                     } else {
                         const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
+                        const bool any_dense4 = k0 == 0xfeu || k1 == 0xfeu || k2 == 0xfeu || k3 == 0xfeu;
                         for (uint32_t rr = warp; rr < rcount; rr += kWarps) {
                             uint4 v = b4;
-                            if (k0 != 0xffu) v.x = sm.patch[k0 * pstride + rr];
-                            if (k1 != 0xffu) v.y = sm.patch[k1 * pstride + rr];
-                            if (k2 != 0xffu) v.z = sm.patch[k2 * pstride + rr];
-                            if (k3 != 0xffu) v.w = sm.patch[k3 * pstride + rr];
+                            if (k0 < 0xfeu) v.x = sm.patch[k0 * pstride + rr];
+                            if (k1 < 0xfeu) v.y = sm.patch[k1 * pstride + rr];
+                            if (k2 < 0xfeu) v.z = sm.patch[k2 * pstride + rr];
+                            if (k3 < 0xfeu) v.w = sm.patch[k3 * pstride + rr];
+                            if (any_dense4) {
+                                // dense words: bit set iff the node's pass count reaches row + 1 (warp-uniform)
+                                const uint32_t thr = r0 + rr + 1;
+                                uint4 ge = make_uint4(~0u, ~0u, ~0u, ~0u);
+#pragma unroll
+                                for (int q = 0; q < 7; ++q) {
+                                    const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lane * 4]);
+                                    if ((thr >> q) & 1u) {
+                                        ge.x &= pl.x; ge.y &= pl.y; ge.z &= pl.z; ge.w &= pl.w;
+                                    } else {
+                                        ge.x |= pl.x; ge.y |= pl.y; ge.z |= pl.z; ge.w |= pl.w;
+                                    }
+                                }
+                                if (k0 == 0xfeu) v.x = ge.x;
+                                if (k1 == 0xfeu) v.y = ge.y;
+                                if (k2 == 0xfeu) v.z = ge.z;
+                                if (k3 == 0xfeu) v.w = ge.w;
+                            }
                             __stcs(reinterpret_cast<uint4*>(dst + toff[r0 + rr]), v);
                         }
                     }
@@ -650,7 +669,19 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                         const uint32_t wl = c * 32 + lane;
                         if (w0 + wl < words_out) {
                             const uint32_t k = sm.pidx[wl];
-                            __stcs(dst + wl, k != 0xffu ? sm.patch[k * pstride + rr] : sm.basew[wl]);
+                            uint32_t v = sm.basew[wl];
+                            if (k < 0xfeu) {
+                                v = sm.patch[k * pstride + rr];
+                            } else if (k == 0xfeu) {
+                                const uint32_t thr = r0 + rr + 1;
+                                v = ~0u;
+#pragma unroll
+                                for (int q = 0; q < 7; ++q) {
+                                    const uint32_t pl = sm.cntp[q * kTileWords + wl];
+                                    v = ((thr >> q) & 1u) ? (v & pl) : (v | pl);
+                                }
+                            }
+                            __stcs(dst + wl, v);
                         }
                     }
                 }
@@ -658,11 +689,9 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         }
         if (tid == 0) {  // everyone copied these to registers before the barriers above (or they are 0)
             sm.n_partial = 0;
-            sm.any_dense = 0;
+            sm.n_dense = 0;
         }
-        if (dbg) dbg[5] = clock64();
         __syncthreads();  // phase A of the next tile rewrites what phase D was reading
-        if (dbg) { unsigned long long g; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g)); dbg[6] = clock64(); dbg[7] = g; }
         cur = nxt;
     }
 }
@@ -736,31 +765,10 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
     // exact t / n_col_blocks as a multiply-high for every t below 2^32 / n_col_blocks (n_tiles is far
     // smaller); 0 stands for "one column block" (2^32 does not fit)
     const uint32_t inv = n_col_blocks == 1 ? 0u : (uint32_t)((0x100000000ull + n_col_blocks - 1) / n_col_blocks);
-    FilterBuffers fbd = fb;
-    fbd.debug_identity = getenv("GS_DEBUG_IDENTITY_PERM") ? 1u : 0u;
-    if (getenv("GS_DEBUG_GRID")) grid = (uint32_t)atoi(getenv("GS_DEBUG_GRID"));
-    static unsigned long long* d_dbg = nullptr;
-    const char* dbg_path = getenv("GS_DEBUG_TIMES");
-    if (dbg_path) {
-        if (!d_dbg) cudaMalloc(&d_dbg, (size_t)4096 * 4 * 8 * 8);
-        cudaMemsetAsync(d_dbg, 0, (size_t)4096 * 4 * 8 * 8, st);
-        fbd.dbg = d_dbg;
-    }
     if (vec)
-        k_expand<true><<<grid, kExpandThreads, 0, st>>>(fbd, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
+        k_expand<true><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
     else
-        k_expand<false><<<grid, kExpandThreads, 0, st>>>(fbd, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
-    if (dbg_path) {
-        cudaStreamSynchronize(st);
-        static unsigned long long h[4096 * 4 * 8];
-        cudaMemcpy(h, d_dbg, sizeof h, cudaMemcpyDeviceToHost);
-        FILE* f = fopen(dbg_path, "wb");
-        if (f) {
-            fwrite(&grid, 4, 1, f);
-            fwrite(h, 8, (size_t)grid * 32, f);
-            fclose(f);
-        }
-    }
+        k_expand<false><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
     return cudaGetLastError();
 }
 

@@ -17,8 +17,6 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     uint32_t* planes;                 // [words / kTileWords][kRankPlanes][kTileWords] node bucket ids, bit-sliced
     unsigned long long* node_key;     // [words * 32] max available memory per node
     uint32_t* sched;                  // [2] tile scheduler of k_expand (self re-arming)
-    unsigned long long* dbg;          // development: per-CTA phase timestamps (nullptr = off)
-    uint32_t debug_identity;          // development knob: ignore perm (wrong rows, timing experiments only)
 };
 cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n, unsigned long long* d_sorted,
                               uint16_t* d_perm, cudaStream_t st);
