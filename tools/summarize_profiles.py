@@ -1,0 +1,53 @@
+#!/usr/bin/env python
+"""Turns gpurun_out/<round>_launches.csv and <round>_expand.ncu-rep into the committed summaries under profiles/."""
+import csv, json, subprocess, sys
+from collections import defaultdict
+
+rnd = sys.argv[1] if len(sys.argv) > 1 else "r01"
+rows = list(csv.reader(open(f"gpurun_out/{rnd}_launches.csv")))
+for i, r in enumerate(rows):
+    if "Kernel Name" in r:
+        hdr, start = r, i
+        break
+ki, mi = hdr.index("Kernel Name"), hdr.index("Metric Value")
+d = defaultdict(list)
+for r in rows[start + 1:]:
+    if len(r) > mi:
+        try:
+            d[r[ki].split("(")[0].replace("void ", "")].append(float(r[mi].replace(",", "")))
+        except ValueError:
+            pass
+lines = ["kernel,launches,mean_us,min_us,max_us,total_us"]
+for k, v in sorted(d.items(), key=lambda kv: -sum(kv[1])):
+    lines.append(f"{k},{len(v)},{sum(v)/len(v)/1e3:.2f},{min(v)/1e3:.2f},{max(v)/1e3:.2f},{sum(v)/1e3:.1f}")
+open(f"profiles/{rnd}_launch_list_summary.csv", "w").write("\n".join(lines) + "\n")
+print("\n".join(lines))
+step = {k: sum(v) / len(v) for k, v in d.items() if any(s in k for s in ("k_prep", "k_group_pods", "k_expand"))}
+tot = sum(step.values())
+share = {k: round(v / tot, 3) for k, v in step.items()}
+raw = subprocess.run(["ncu", "-i", f"gpurun_out/{rnd}_expand.ncu-rep", "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rr = list(csv.reader(raw.splitlines()))
+h, u = rr[0], rr[1]
+want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_sectors_op_write.sum", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "launch__registers_per_thread", "launch__grid_size", "smsp__inst_executed.sum", "sm__cycles_elapsed.max", "sm__cycles_active.avg",
+        "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers", "smsp__sass_inst_executed_op_global_st.sum"]
+def tobytes(v, unit):
+    f = float(v.replace(",", ""))
+    return f * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
+launches = []
+for r in rr[2:]:
+    m = {}
+    for w in want:
+        if w in h:
+            i = h.index(w)
+            m[w] = tobytes(r[i], u[i]) if "bytes" in w else float(r[i].replace(",", ""))
+    launches.append(m)
+dram = [m["dram__bytes_read.sum"] + m["dram__bytes_write.sum"] for m in launches]
+out = {"round": rnd, "kernel": "k_expand<true>", "command": "python bench.py --steps 5 --warmup 3 --no-cpu-baseline (ncu --set full --clock-control none -k regex:k_expand -s 4 -c 2)",
+       "dram_bytes_per_launch": sum(dram) / len(dram), "launches": launches,
+       "filter_step_kernel_share_ncu": share,
+       "note": "ncu serialises launches and flushes caches: the 62.7 MB bitmap stays in the 126 MB L2 for the duration of one isolated launch, so dram bytes are far below the algorithmic bytes; compare shares, not absolutes"}
+json.dump(out, open("profiles/expand_ncu_summary.json", "w"), indent=1)
+print(json.dumps({k: out[k] for k in ("dram_bytes_per_launch", "filter_step_kernel_share_ncu")}, indent=1))
+print({k: launches[0].get(k) for k in want})
