@@ -11,7 +11,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libgpushare_b200.so")
 
-SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu"]
+SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu", "noalloc.cu"]
 HEADERS = ["common.cuh", "kernels.h", "exports.map", os.path.join(ROOT, "include", "gpushare_b200.h")]
 
 NVCC_FLAGS = [

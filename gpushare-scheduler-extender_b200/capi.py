@@ -37,7 +37,7 @@ EXPORTS = [
     "gs_node_upsert", "gs_node_count", "gs_pods_load", "gs_rebuild", "gs_pods_apply", "gs_filter_batch",
     "gs_filter_batch_device", "gs_filter_stages_device", "gs_node_classes", "gs_bind_batch", "gs_bind_rollback", "gs_inspect",
     "gs_read_used", "gs_read_pods", "gs_host_alloc", "gs_host_free", "gs_profile_enable", "gs_profile_read",
-    "gs_profile_reset", "gs_launch_count", "gs_device_ptrs",
+    "gs_profile_reset", "gs_launch_count", "gs_device_ptrs", "gs_pods_apply_static",
 ]
 
 
@@ -93,6 +93,7 @@ def load():
         "gs_profile_reset": (C.c_int, [vp]),
         "gs_launch_count": (C.c_int, [vp, u64p]),
         "gs_device_ptrs": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+        "gs_pods_apply_static": (C.c_int, [C.c_int, vp, u32, vp, u32, vp, u32, u32, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -268,11 +269,28 @@ class Snapshot:
             res[name] = (n.value, ms.value)
         return res
 
+    def device_ptrs(self) -> dict:
+        """Device addresses of the snapshot arrays (gs_device_ptrs)."""
+        p = [C.c_void_p() for _ in range(4)]
+        _check(load().gs_device_ptrs(self.h, *[C.byref(x) for x in p]))
+        return dict(used=p[0].value, capacity=p[1].value, nodeinfo=p[2].value, pods=p[3].value)
+
     @property
     def launch_count(self) -> int:
         v = C.c_uint64()
         _check(load().gs_launch_count(self.h, C.byref(v)))
         return v.value
+
+
+STATIC_MAX_SLOTS = 1 << 20
+
+
+def pods_apply_static(device: int, d_events: int, n_events: int, d_pods: int, n_slots: int, d_nodeinfo: int,
+                      n_nodes: int, dev_stride: int, d_used: int, stream: int = 0):
+    """gs_pods_apply_static: every argument is a device address the caller owns; nothing is allocated."""
+    _check(load().gs_pods_apply_static(device, C.c_void_p(d_events), n_events, C.c_void_p(d_pods), n_slots,
+                                       C.c_void_p(d_nodeinfo), n_nodes, dev_stride, C.c_void_p(d_used),
+                                       C.c_void_p(stream)))
 
 
 def unpack_bitmap(bitmap: np.ndarray, n_nodes: int) -> np.ndarray:

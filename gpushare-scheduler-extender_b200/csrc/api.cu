@@ -31,6 +31,10 @@ static int cuda_fail(cudaError_t e, const char* what) {
         if (e_ != cudaSuccess) return cuda_fail(e_, #call); \
     } while (0)
 
+namespace gs {
+void set_last_error(const char* msg) { snprintf(g_err, sizeof g_err, "%s", msg); }
+}  // namespace gs
+
 namespace {
 
 struct Guard {

@@ -7,6 +7,9 @@
 
 namespace gs {
 
+// message returned by gs_last_error() on the calling thread (api.cu)
+void set_last_error(const char* msg);
+
 // K3 (filter_kernels.cu)
 struct FilterBuffers {              // work buffers of one filter launch sequence (HBM scratch)
     unsigned long long* grouped_req;  // [GS_MAX_BATCH] requests in bucket order

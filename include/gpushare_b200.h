@@ -208,6 +208,34 @@ int gs_launch_count(gs_snapshot* s, uint64_t* out_launches);
 /* Device pointers of the snapshot arrays, for zero-copy use from the same process (tests, NCCL). */
 int gs_device_ptrs(gs_snapshot* s, void** d_used, void** d_capacity, void** d_nodeinfo, void** d_pods);
 
+/* Pod events for callers that must not allocate.  (No counterpart in the reference: this exists only
+ * because some hosts of this library cannot call cudaMalloc.)
+ *
+ * gs_pods_apply copies its events to the GPU and may grow a staging buffer, so it can call cudaMalloc /
+ * cudaMallocHost.  A host that has given all GPU memory to one owner at start-up and forbids later
+ * allocation -- or that sits on a path where the device-wide synchronisation hidden in cudaMalloc and
+ * cudaFree is unacceptable -- uses this entry point instead: it calls no allocating routine at all.
+ * The caller passes device pointers it already owns for everything:
+ *   d_events   [n_events]            the batch, same meaning and order rules as gs_pods_apply
+ *   d_pods     [n_slots]             the pod table, updated in place
+ *   d_nodeinfo [n_nodes]             one word per node: dev_count | (GS_NODE_* class << 16)
+ *   d_used     [n_nodes][dev_stride] used memory per device, updated in place
+ * (the arrays of a snapshot, from gs_device_ptrs, qualify).  The only scratch -- one int32 per pod slot
+ * -- is a fixed array of GS_STATIC_MAX_SLOTS entries (4 MiB) inside the library; every GPU that loads
+ * the library holds it until the process exits.  n_slots above GS_STATIC_MAX_SLOTS is refused with
+ * GS_ERR_CAPACITY.
+ *
+ * The first call on a device looks up the array's device address (cudaGetSymbolAddress, once per
+ * device); make that first call before any CUDA stream capture begins.  The work is queued on
+ * `cuda_stream` (NULL = the default stream) and the call returns without waiting for it.  All calls on
+ * one GPU share the one array, which keeps what the last call left in it: the entry point resets the
+ * part it is about to use at the start of every call, and two calls whose kernels overlap on the GPU
+ * (different streams, different threads) race on it -- order them on one stream or with events. */
+#define GS_STATIC_MAX_SLOTS (1u << 20)
+int gs_pods_apply_static(int device, const gs_pod_event* d_events, uint32_t n_events, gs_pod_record* d_pods,
+                         uint32_t n_slots, const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride,
+                         uint64_t* d_used, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
