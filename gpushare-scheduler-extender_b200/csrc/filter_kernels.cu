@@ -375,7 +375,7 @@ struct ExpandSmem {
     uint8_t plist[kTileWords];          // words that need per-row values
     uint8_t pidx[kTileWords];           // position in plist, 0xff = the word is the same in every row
     uint8_t dlist[kTileWords];          // the dense ones among them
-    uint32_t n_partial, n_dense;
+    uint32_t n_partial, n_dense, next_tile;
 };
 
 // Inputs of one tile, brought in by bulk asynchronous copies (TMA) that complete on an mbarrier.  They
@@ -447,8 +447,11 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         bulk_load(in.bucket, fb.row_bucket + j0, sizeof(in.bucket), &tin_bar[stage]);
     };
 
-    // Static round-robin tile schedule: tile numbers blockIdx.x + it * gridDim.x.  (A dynamic ticket
-    // scheduler with look-ahead hoards tickets when there are only ~3 tiles per CTA: profiles/NOTES.md.)
+    // Tile schedule: the first tile of a CTA is blockIdx.x; every later one is a ticket taken late in
+    // the current tile (after its dense work, if any), so a CTA never holds more than one tile ahead and
+    // CTAs stuck in a dense tile simply take fewer.  (Tickets taken several tiles ahead hoard when there
+    // are only ~3 tiles per CTA: profiles/NOTES.md.)
+    uint32_t ticket = 0;  // thread 0
     if (tid == 0) {
 #pragma unroll
         for (int i = 0; i < kPrefetch; ++i) mbar_init(&tin_bar[i], 1);
@@ -457,8 +460,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         sm.n_partial = 0;
         sm.n_dense = 0;
-#pragma unroll
-        for (int i = 0; i < kPrefetch; ++i) request(blockIdx.x + i * gridDim.x, i);
+        request(blockIdx.x, 0);
     }
     __syncthreads();
     uint32_t cur = blockIdx.x;
@@ -521,11 +523,10 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         }
         __syncthreads();  // phase A results are visible; nobody reads this stage's inputs any more
 
-        const uint32_t nxt = cur + gridDim.x;
         const uint32_t np = sm.n_partial;
         const uint32_t nd = sm.n_dense;
         const bool dense = nd != 0;
-        if (tid == 0) request(cur + kPrefetch * gridDim.x, stage);  // refill the stage just consumed
+        if (!dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);  // consumed just before phase D
 
         // Words with many compared nodes want the tile's rows in ascending request order: then a node's
         // column is a prefix of ones and one binary search per node replaces a comparison per row.
@@ -560,30 +561,48 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                 if (half) fetch_keys(half);
                 mbar_wait(&key_bar, key_phase);
                 key_phase ^= 1u;
-                for (uint32_t i = warp; i < 64; i += kWarps) {
-                    const uint32_t t = half * 64 + i;
-                    if (sm.pidx[t] != 0xfeu) continue;  // warp-uniform
-                    const u64 mykey = kstage[i * 32 + lane];
-                    // cnt = #{rows : req <= key}: branch-free upper bound over the 64 sorted requests
-                    uint32_t cnt = 0;
+                // each warp owns words warp, warp + 8, ... of this half and runs four of them at a time, so
+                // that four independent binary searches hide each other's shared-memory latency
+                for (uint32_t i0 = warp; i0 < 64; i0 += 4 * kWarps) {
+                    uint32_t cnt[4];
+                    u64 key[4];
+                    bool on[4];
 #pragma unroll
-                    for (uint32_t step = kTileRows / 2; step > 0; step >>= 1)
-                        if (sm.req_sorted[cnt + step - 1] <= mykey) cnt += step;
-                    if (cnt == kTileRows - 1 && sm.req_sorted[kTileRows - 1] <= mykey) cnt = kTileRows;
-                    cnt = min(cnt, rows);  // a key of ~0 also matches the padding rows
-                    // nodes outside `some` never pass (q' == 0 stores key 0, which would match a zero request)
-                    if (!((sm.somew[t] >> lane) & 1u)) cnt = 0;
-                    uint32_t mine = 0;
-#pragma unroll
-                    for (int q = 0; q < 7; ++q) {
-                        const uint32_t bal = __ballot_sync(0xffffffffu, (cnt >> q) & 1u);
-                        if ((int)lane == q) mine = bal;
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t i = i0 + u * kWarps;
+                        on[u] = i < 64 && sm.pidx[half * 64 + i] == 0xfeu;  // warp-uniform
+                        key[u] = on[u] ? kstage[i * 32 + lane] : 0ull;
+                        cnt[u] = 0;
                     }
-                    if (lane < 7) sm.cntp[lane * kTileWords + t] = mine;  // plane-major
+                    // cnt = #{rows : req <= key}: branch-free upper bound over the 64 sorted requests
+#pragma unroll
+                    for (uint32_t step = kTileRows / 2; step > 0; step >>= 1) {
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (sm.req_sorted[cnt[u] + step - 1] <= key[u]) cnt[u] += step;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (!on[u]) continue;
+                        const uint32_t t = half * 64 + i0 + u * kWarps;
+                        uint32_t c = cnt[u];
+                        if (c == kTileRows - 1 && sm.req_sorted[kTileRows - 1] <= key[u]) c = kTileRows;
+                        c = min(c, rows);  // a key of ~0 also matches the padding rows
+                        // nodes outside `some` never pass (q' == 0 stores key 0, which would match a zero request)
+                        if (!((sm.somew[t] >> lane) & 1u)) c = 0;
+                        uint32_t mine = 0;
+#pragma unroll
+                        for (int q = 0; q < 7; ++q) {
+                            const uint32_t bal = __ballot_sync(0xffffffffu, (c >> q) & 1u);
+                            if ((int)lane == q) mine = bal;
+                        }
+                        if (lane < 7) sm.cntp[lane * kTileWords + t] = mine;  // plane-major
+                    }
                 }
                 __syncthreads();  // the staging area is reused (second half, then the patch)
             }
         }
+        if (dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);
         // rows per sub-pass so that np patched words x rows fit the patch (odd stride spreads banks)
         uint32_t pstride = np ? kPatchWords / np : kPatchWords;
         pstride -= (pstride & 1u) ^ 1u;
@@ -617,6 +636,10 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     }
                 }
                 __syncthreads();
+            }
+            if (r0 == 0 && tid == 0) {  // the next tile is known: start fetching its inputs
+                sm.next_tile = gridDim.x + ticket;
+                request(sm.next_tile, stage ^ 1u);
             }
             // D: lane owns 4 words, warp owns rows r0 + warp, r0 + warp + kWarps, ...; 16 bytes per
             // lane, 512 contiguous bytes per warp and row
@@ -692,7 +715,15 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             sm.n_dense = 0;
         }
         __syncthreads();  // phase A of the next tile rewrites what phase D was reading
-        cur = nxt;
+        cur = sm.next_tile;
+    }
+    // the last CTA out re-arms the ticket counter for the next launch
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(&fb.sched[1], 1u) == gridDim.x - 1) {
+            fb.sched[0] = 0;
+            fb.sched[1] = 0;
+        }
     }
 }
 
@@ -759,9 +790,7 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
     const uint32_t per_sm = 5;  // resident CTAs per SM (256 threads, 48 registers, 42 KB shared)
     uint32_t grid = (uint32_t)sm_count * per_sm;
     if (grid > n_tiles) grid = n_tiles;
-    // static schedule: the smallest grid that gives the same number of rounds, so all CTAs get the same share
-    const uint32_t rounds = (n_tiles + grid - 1) / grid;
-    grid = (n_tiles + rounds - 1) / rounds;
+
     // exact t / n_col_blocks as a multiply-high for every t below 2^32 / n_col_blocks (n_tiles is far
     // smaller); 0 stands for "one column block" (2^32 does not fit)
     const uint32_t inv = n_col_blocks == 1 ? 0u : (uint32_t)((0x100000000ull + n_col_blocks - 1) / n_col_blocks);
