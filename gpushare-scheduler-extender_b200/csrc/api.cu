@@ -149,7 +149,6 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     fb.grouped_req = s->d_sorted_keys;
     fb.perm = s->d_perm;
     fb.row_bucket = s->d_row_bucket;
-    fb.pod_slot = s->d_pod_slot;
     fb.pod_hist = s->d_pod_hist;
     fb.planes = s->d_rank_planes;
     fb.node_key = s->d_node_key;
@@ -161,7 +160,7 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     int rc = GS_OK;
     const bool do_pods = (stages & GS_STAGE_SORT) != 0, do_nodes = (stages & GS_STAGE_NODE_RANK) != 0;
     if (do_pods || do_nodes)
-        rc = timed(s, do_pods ? GS_K_SORT : GS_K_NODE_RANK, st, do_pods ? 2 : 1, [&] {
+        rc = timed(s, do_pods ? GS_K_SORT : GS_K_NODE_RANK, st, 1, [&] {
             return gs::launch_prep(d_req, n_pods, do_pods, do_nodes, shift, fb, s->d_used, s->d_cap, s->d_nodeinfo,
                                    s->n_nodes, s->max_devs, words_pad, st);
         });
@@ -245,9 +244,8 @@ int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32
     CU_NEW(cudaMalloc(&s->d_rank_planes, (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t)));
     CU_NEW(cudaMalloc(&s->d_node_key, (size_t)s->rank_words * 32 * sizeof(u64)));
     CU_NEW(cudaMalloc(&s->d_row_bucket, (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
-    CU_NEW(cudaMalloc(&s->d_pod_slot, (size_t)GS_MAX_BATCH * sizeof(uint32_t)));
-    CU_NEW(cudaMalloc(&s->d_pod_hist, 513 * sizeof(uint32_t)));
-    CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 513 * sizeof(uint32_t), s->stream));
+    CU_NEW(cudaMalloc(&s->d_pod_hist, 516 * sizeof(uint32_t)));
+    CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 516 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMalloc(&s->d_sched, 2 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_sched, 0, 2 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_used, 0, (size_t)max_nodes * max_devs * sizeof(u64), s->stream));
@@ -277,7 +275,6 @@ int gs_snapshot_destroy(gs_snapshot* s) {
     cudaFree(s->d_rank_planes);
     cudaFree(s->d_node_key);
     cudaFree(s->d_row_bucket);
-    cudaFree(s->d_pod_slot);
     cudaFree(s->d_pod_hist);
     cudaFree(s->d_sched);
     cudaFree(s->d_stage);

@@ -203,9 +203,10 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
 // derived on the host from the largest device capacity ever upserted, so requests up to that capacity
 // spread over all buckets; the last bucket is open-ended.  Bucket ids are stored 1-based.
 //
-// Pod blocks: first half of grouping the pending pods by bucket: every pod takes an arrival number in
-// its bucket with an L2 atomic.  k_group_pods then turns the bucket counts into offsets and writes the
-// grouped order.  Order inside a bucket is whatever the atomics give; the bitmap does not depend on it.
+// Pod blocks: group the pending pods by bucket: every pod takes an arrival number in its bucket with an
+// L2 atomic; after a barrier among the pod blocks each block turns the bucket counts into offsets and
+// writes the grouped position of its own pods.  Order inside a bucket is whatever the atomics give; the
+// bitmap does not depend on it.
 //
 // Node blocks: one warp per 32-node word, lane = node.  key = max available memory over the node's
 // devices (nodeinfo.go:254-264, u64 wrap-around included) and
@@ -232,16 +233,72 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
        const u64* __restrict__ used, const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
        uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // programmatic dependent launch: k_expand may start its prologue now; it waits (griddepcontrol.wait)
+    // for this grid to complete before it reads anything written here
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (blockIdx.x < pod_blocks) {
         // ---------------- pod role ----------------
-        uint32_t* ghist = fb.pod_hist;        // [kBuckets] + [1] finished-blocks counter
-        uint32_t* slots = fb.pod_slot;        // [GS_MAX_BATCH] (bucket << 16) | arrival number
+        __shared__ uint32_t base[kBuckets];
+        __shared__ uint32_t wsum[kPrepThreads / 32];
+        __shared__ bool is_last;
+        static_assert(kPrepThreads == (int)kBuckets, "one bucket per thread in the scan");
+        uint32_t* ghist = fb.pod_hist;  // [kBuckets] counts, [kBuckets] arrived blocks, [kBuckets + 1] finished blocks
         const uint32_t i = blockIdx.x * kPrepThreads + tid;
+        uint32_t sl = 0;
+        u64 r = 0;
         if (i < n_pods) {
-            const u64 r = req[i];
+            r = req[i];
             const u64 bq = r >> shift;
             const uint32_t b = bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1;
-            slots[i] = (b << 16) | atomicAdd(&ghist[b], 1u);
+            sl = (b << 16) | atomicAdd(&ghist[b], 1u);  // arrival number inside the bucket
+        }
+        // barrier among the pod blocks (they are the first blocks of a grid far smaller than the GPU, so
+        // all of them are resident): the bucket counts are complete once every block has arrived
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            atomicAdd(&ghist[kBuckets], 1u);
+            while (atomicAdd(&ghist[kBuckets], 0u) < pod_blocks) {
+            }
+            __threadfence();
+        }
+        __syncthreads();
+        // bucket counts -> offsets (every block scans the 512 counts itself), then the block's own pods
+        const uint32_t cnt = __ldcg(&ghist[tid]);
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((int)lane >= o) incl += t;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t w = lane < kPrepThreads / 32 ? wsum[lane] : 0u;
+            uint32_t wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+                if ((int)lane >= o) wi += t;
+            }
+            if (lane < kPrepThreads / 32) wsum[lane] = wi - w;
+        }
+        __syncthreads();
+        base[tid] = wsum[warp] + incl - cnt;
+        __syncthreads();
+        if (i < n_pods) {
+            const uint32_t b = sl >> 16;
+            const uint32_t j = base[b] + (sl & 0xffffu);
+            fb.perm[j] = (uint16_t)i;
+            fb.grouped_req[j] = r;
+            fb.row_bucket[j] = (uint16_t)(b + 1);  // bucket ids are stored 1-based
+        }
+        // every block has read the counts once it is here; the last one out re-arms them
+        if (tid == 0) is_last = atomicAdd(&ghist[kBuckets + 1], 1u) == pod_blocks - 1;
+        __syncthreads();
+        if (is_last) {
+            ghist[tid] = 0;
+            if (tid < 2) ghist[kBuckets + tid] = 0;
         }
         return;
     }
@@ -281,62 +338,6 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
     }
     if (lane < kRankPlanes)
         fb.planes[((size_t)(word / kTileWords) * kRankPlanes + lane) * kTileWords + (word % kTileWords)] = mine;
-}
-
-// Second half of the pod side: bucket counts -> offsets (every block scans the 512 counts itself),
-// then each block writes the grouped position of its own pods.  The last block out re-arms the counts.
-__global__ void __launch_bounds__(kPrepThreads)
-k_group_pods(const u64* __restrict__ req, uint32_t n_pods, FilterBuffers fb) {
-    __shared__ uint32_t base[kBuckets];
-    __shared__ uint32_t wsum[kPrepThreads / 32];
-    __shared__ bool is_last;
-    static_assert(kPrepThreads == (int)kBuckets, "one bucket per thread in the scan");
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint32_t* ghist = fb.pod_hist;
-    const uint32_t p = blockIdx.x * kPrepThreads + tid;
-    uint32_t sl = 0;
-    u64 r = 0;
-    if (p < n_pods) {
-        sl = fb.pod_slot[p];
-        r = req[p];
-    }
-    const uint32_t cnt = ghist[tid];
-    uint32_t incl = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if ((int)lane >= o) incl += t;
-    }
-    if (lane == 31) wsum[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-        const uint32_t w = lane < kPrepThreads / 32 ? wsum[lane] : 0u;
-        uint32_t wi = w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
-            if ((int)lane >= o) wi += t;
-        }
-        if (lane < kPrepThreads / 32) wsum[lane] = wi - w;
-    }
-    __syncthreads();
-    base[tid] = wsum[warp] + incl - cnt;
-    __syncthreads();
-    if (p < n_pods) {
-        const uint32_t b = sl >> 16;
-        const uint32_t j = base[b] + (sl & 0xffffu);
-        fb.perm[j] = (uint16_t)p;
-        fb.grouped_req[j] = r;
-        fb.row_bucket[j] = (uint16_t)(b + 1);
-    }
-    // every block has read the counts once it is here; the last one out clears them
-    __syncthreads();
-    if (tid == 0) is_last = atomicAdd(&ghist[kBuckets], 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (is_last) {
-        ghist[tid] = 0;
-        if (tid == 0) ghist[kBuckets] = 0;
-    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -460,8 +461,10 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         sm.n_partial = 0;
         sm.n_dense = 0;
-        request(blockIdx.x, 0);
     }
+    // everything above overlapped the tail of k_prep; its results are needed from here on
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (tid == 0) request(blockIdx.x, 0);
     __syncthreads();
     uint32_t cur = blockIdx.x;
 
@@ -767,9 +770,6 @@ cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do
     else
         k_prep<0><<<pod_blocks + node_blocks, kPrepThreads, 0, st>>>(d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap,
                                                                      d_nodeinfo, n_nodes, dev_stride, n_words);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess || pod_blocks == 0) return e;
-    k_group_pods<<<pod_blocks, kPrepThreads, 0, st>>>(d_req, n_pods, fb);
     return cudaGetLastError();
 }
 
@@ -794,11 +794,19 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
     // exact t / n_col_blocks as a multiply-high for every t below 2^32 / n_col_blocks (n_tiles is far
     // smaller); 0 stands for "one column block" (2^32 does not fit)
     const uint32_t inv = n_col_blocks == 1 ? 0u : (uint32_t)((0x100000000ull + n_col_blocks - 1) / n_col_blocks);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kExpandThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // overlap the launch with k_prep's tail
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
     if (vec)
-        k_expand<true><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
-    else
-        k_expand<false><<<grid, kExpandThreads, 0, st>>>(fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
-    return cudaGetLastError();
+        return cudaLaunchKernelEx(&cfg, k_expand<true>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
+    return cudaLaunchKernelEx(&cfg, k_expand<false>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
 }
 
 }  // namespace gs
