@@ -179,8 +179,8 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "nodes": sc.n_nodes, "devices_per_node": sc.max_devs, "running_pods": sc.n_pods,
-                   "pending_pods": len(reqs), "requests": REQ_KIND, "sample": sample},
+        "config": {"workload": WORKLOAD, "nodes_per_gpu": sc.n_nodes, "devices_per_node": sc.max_devs,
+                   "running_pods_per_gpu": sc.n_pods, "pending_pods": len(reqs), "requests": REQ_KIND, "sample": sample},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -270,7 +270,8 @@ def run_product(args):
     # per-kernel device times: CUDA events on the launching stream around `steps` back-to-back launches
     # of ONE stage (same inputs, same rotating outputs); the stages of a step sum to ~ms_per_step
     kernel_ms = {}
-    for name, mask in (("sort", gsx.capi.STAGE_SORT), ("node_rank", gsx.capi.STAGE_NODE_RANK), ("expand", gsx.capi.STAGE_EXPAND)):
+    for name, mask in (("prep_pods", gsx.capi.STAGE_SORT), ("prep_nodes", gsx.capi.STAGE_NODE_RANK),
+                       ("prep", gsx.capi.STAGE_SORT | gsx.capi.STAGE_NODE_RANK), ("expand", gsx.capi.STAGE_EXPAND)):
         for i in range(3):
             snap.filter_stages_device(mask, d_req.data_ptr(), P, outs[i % N_OUT_BUFFERS].data_ptr(), stride, stream)
         torch.cuda.synchronize()
@@ -283,13 +284,16 @@ def run_product(args):
         kernel_ms[name] = k0.elapsed_time(k1) / args.steps
     t_expand = kernel_ms.get("expand")
     words_pad = (words + 127) // 128 * 128
-    expand_bytes = P * words * 4 + words_pad * 64 + P * 2       # bitmap written + rank planes + row permutation
+    expand_bytes = P * words * 4 + words_pad * 40 + P * 12      # bitmap written + node bucket planes + per-row request/perm/bucket
     step_bytes = N * sc.max_devs * 8 + N * 8 + N * 4 + P * 8 + P * words * 4
     peak, peak_src = _peaks()
     achieved = expand_bytes / (t_expand * 1e-3) / 1e9 if t_expand else None
     roofline = {"bound": "hbm", "kernel": "k_expand", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": _traffic(), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": expand_bytes, "kernel_ms": t_expand,
+                "note": "the 62.7 MB bitmap fits the 126 MB L2, so `traffic` (ncu, one isolated launch) is far below the algorithmic bytes; "
+                        "in this run four output buffers rotate so every step's lines reach DRAM; a plain streaming store of the same "
+                        "rows takes 12.3 us on this GPU (profiles/NOTES.md)",
                 "step_algorithmic_bytes": step_bytes,
                 "step_achieved_gbs": step_bytes / (ms_per_step * 1e-3) / 1e9}
 

@@ -22,7 +22,7 @@ for k, v in sorted(d.items(), key=lambda kv: -sum(kv[1])):
     lines.append(f"{k},{len(v)},{sum(v)/len(v)/1e3:.2f},{min(v)/1e3:.2f},{max(v)/1e3:.2f},{sum(v)/1e3:.1f}")
 open(f"profiles/{rnd}_launch_list_summary.csv", "w").write("\n".join(lines) + "\n")
 print("\n".join(lines))
-step = {k: sum(v) / len(v) for k, v in d.items() if any(s in k for s in ("k_prep", "k_group_pods", "k_expand"))}
+step = {k: sum(v) / len(v) for k, v in d.items() if any(s in k for s in ("k_prep", "k_expand"))}
 tot = sum(step.values())
 share = {k: round(v / tot, 3) for k, v in step.items()}
 raw = subprocess.run(["ncu", "-i", f"gpurun_out/{rnd}_expand.ncu-rep", "--page", "raw", "--csv"], capture_output=True, text=True).stdout
