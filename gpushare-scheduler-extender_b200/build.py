@@ -11,8 +11,9 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libgpushare_b200.so")
 
-SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu", "noalloc.cu"]
-HEADERS = ["common.cuh", "kernels.h", "exports.map", os.path.join(ROOT, "include", "gpushare_b200.h")]
+SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu", "noalloc.cu", "ext.cpp"]
+HEADERS = ["common.cuh", "kernels.h", "exports.map", "ext_state.inc", "ext_handlers.inc",
+           os.path.join(ROOT, "include", "gpushare_ext.h"), os.path.join(ROOT, "include", "gpushare_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -44,7 +45,7 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
     objs = []
     for src in SOURCES:
-        obj = os.path.join(LIB_DIR, src.replace(".cu", ".o"))
+        obj = os.path.join(LIB_DIR, os.path.splitext(src)[0] + ".o")
         cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")

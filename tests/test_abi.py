@@ -11,13 +11,15 @@ import gsx
 from gsx import capi
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-HEADER = os.path.join(ROOT, "include", "gpushare_b200.h")
+HEADERS = [os.path.join(ROOT, "include", "gpushare_b200.h"), os.path.join(ROOT, "include", "gpushare_ext.h")]
 
 
 def declared():
-    src = open(HEADER).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(gs_[a-z0-9_]+)\s*\(", src)))
+    names = set()
+    for h in HEADERS:
+        src = re.sub(r"/\*.*?\*/", "", open(h).read(), flags=re.S)
+        names |= set(re.findall(r"\b(gs_[a-z0-9_]+)\s*\(", src))
+    return sorted(names)
 
 
 def test_header_symbols_are_exported():
@@ -29,7 +31,7 @@ def test_header_symbols_are_exported():
     out = subprocess.run(["nm", "-D", "--defined-only", capi.library_path()], capture_output=True, text=True).stdout
     exported = sorted(l.split()[-1] for l in out.splitlines() if " T " in l)
     assert exported == names, "exports and header disagree"
-    assert sorted(capi.EXPORTS) == names
+    assert sorted(capi.EXPORTS + gsx.ext.EXPORTS) == names
 
 
 def test_struct_layouts_match_header(tmp_path):
