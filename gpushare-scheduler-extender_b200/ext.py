@@ -50,6 +50,11 @@ def lib():
         "gs_ext_filter_codes": (C.c_int, [vp, C.POINTER(vp), sz, C.POINTER(cp), sz, C.POINTER(C.c_uint8)]),
         "gs_ext_bind": (C.c_int, [vp, cp, cp, cp, cp, C.c_int, C.POINTER(i64), cp, sz]),
         "gs_ext_inspect_node": (C.c_int, [vp, cp, C.POINTER(u64), C.POINTER(u64), C.c_int, cp, sz]),
+        "gs_ext_informer_add": (C.c_int, [vp, vp]),
+        "gs_ext_informer_update": (C.c_int, [vp, vp, vp]),
+        "gs_ext_informer_delete": (C.c_int, [vp, vp]),
+        "gs_ext_ctrl_drain": (C.c_int, [vp]),
+        "gs_ext_ctrl_queue_len": (sz, [vp]),
         "gs_ext_free": (None, [vp]),
     }
     for name, (res, args) in sig.items():
@@ -66,7 +71,8 @@ EXPORTS = ["gs_ext_pod_new", "gs_ext_pod_free", "gs_ext_pod_set_node_name", "gs_
            "gs_ext_node_lister_set", "gs_ext_node_lister_delete", "gs_ext_pod_lister_set", "gs_ext_pod_lister_delete",
            "gs_ext_api_set_pod", "gs_ext_get_node_info", "gs_ext_build_cache", "gs_ext_add_or_update_pod",
            "gs_ext_remove_pod", "gs_ext_known_pod", "gs_ext_filter_json", "gs_ext_filter_codes", "gs_ext_bind",
-           "gs_ext_inspect_node", "gs_ext_free"]
+           "gs_ext_inspect_node", "gs_ext_free", "gs_ext_informer_add", "gs_ext_informer_update",
+           "gs_ext_informer_delete", "gs_ext_ctrl_drain", "gs_ext_ctrl_queue_len"]
 
 
 def _b(s: str) -> bytes:
@@ -196,6 +202,22 @@ class Extender:
         self._buf.value = b""
         rc = lib().gs_ext_bind(self.h, _b(pod_name), _b(ns), _b(uid), _b(node), api_mode, C.byref(dev), self._buf, len(self._buf))
         return dev.value, ("" if rc == 0 else self._buf.value.decode())
+
+    def informer_add(self, pod: Pod):
+        lib().gs_ext_informer_add(self.h, pod.h)
+
+    def informer_update(self, old: Pod, new: Pod):
+        lib().gs_ext_informer_update(self.h, old.h, new.h)
+
+    def informer_delete(self, pod: Pod):
+        lib().gs_ext_informer_delete(self.h, pod.h)
+
+    def drain(self):
+        return None if lib().gs_ext_ctrl_drain(self.h) == 0 else _err()
+
+    @property
+    def queue_len(self):
+        return lib().gs_ext_ctrl_queue_len(self.h)
 
     def inspect_node(self, name, cap=64):
         total, used = (C.c_uint64 * cap)(), (C.c_uint64 * cap)()

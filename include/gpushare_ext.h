@@ -18,6 +18,7 @@
  *                                     gpushare-predicate.go:16-37        | gs_ext_filter_codes
  *   Bind.Handler + NodeInfo.Allocate  pkg/scheduler/gpushare-bind.go:21-65, pkg/cache/nodeinfo.go:139-206 | gs_ext_bind
  *   Inspect buildNode                 pkg/scheduler/inspect.go:33-71     | gs_ext_inspect_node
+ *   informer handlers + syncPod       pkg/gpushare/controller.go:77-100,174-332 | gs_ext_informer_*, gs_ext_ctrl_drain
  *   utils.* parsers                   pkg/utils/pod.go:45-60,94-113,146-155 | gs_ext_pod_* getters
  *
  * All decisions (pass sets, chosen devices, used memory) come from the CUDA kernels; this layer only
@@ -93,6 +94,15 @@ int gs_ext_bind(gs_ext* x, const char* pod_name, const char* pod_ns, const char*
                 int api_mode, int64_t* dev_id, char* err, size_t errcap);
 /* Inspect: per-device total/used of a cached node; returns gpu-count, or -1 with err. */
 int gs_ext_inspect_node(gs_ext* x, const char* name, uint64_t* total, uint64_t* used, int cap, char* err, size_t errcap);
+
+/* Event path (pkg/gpushare/controller.go:77-100,174-332): informer handlers behind the IsGPUsharingPod filter, the
+ * work queue, and syncPod.  Update the pod lister first, as the informer does, then report the event;
+ * gs_ext_ctrl_drain runs syncPod for every queued key. */
+int gs_ext_informer_add(gs_ext* x, const gs_ext_pod* p);
+int gs_ext_informer_update(gs_ext* x, const gs_ext_pod* old_p, const gs_ext_pod* new_p);
+int gs_ext_informer_delete(gs_ext* x, const gs_ext_pod* p);
+int gs_ext_ctrl_drain(gs_ext* x);
+size_t gs_ext_ctrl_queue_len(gs_ext* x);
 
 void gs_ext_free(void* p);
 

@@ -111,3 +111,53 @@ def test_random_operation_sequences(seed):
         pods_x = [X.Pod(f"q{i}", limits=[int(r)]) for i, r in enumerate([0, 512, 5000, 9000, 16384, 17000])]
         pods_o = [O.Pod(f"q{i}", limits=[int(r)]) for i, r in enumerate([0, 512, 5000, 9000, 16384, 17000])]
         assert (xe.filter_codes(pods_x, names + ["ghost"]) == oc.filter_many(pods_o, names + ["ghost"])).all()
+
+
+def test_event_path_matches_oracle():
+    """Informer events -> filter -> queue -> syncPod (pkg/gpushare/controller.go:77-100,174-332): the same random
+    stream of pod creations, annotation updates (as a Bind would write them), phase changes and deletions goes to
+    the mirror and to the oracle; queue lengths, knownPods and per-device used memory must agree after each drain."""
+    rng = np.random.default_rng(11)
+    names = [f"node-{i:02d}" for i in range(6)]
+    oc = O.Cluster()
+    with X.Extender(16, 4, 1024) as xe:
+        for n in names:
+            xe.set_node(n, mem=16384 * 4, count=4)
+            oc.set_node(n, mem=16384 * 4, count=4)
+        state = {}                                                # name -> kwargs of the listed pod
+        for step in range(400):
+            name = f"p{int(rng.integers(0, 40))}"
+            old = state.get(name)
+            u = rng.random()
+            if old is None:
+                kw = dict(uid=f"U-{name}-{step}", limits=[int(rng.choice([0, 1024, 4096]))])
+                px, po = both_pods(name, **kw)
+                xe.list_pod(px); oc.list_pod(po)
+                xe.informer_add(px); oc.informer_add(po)
+                state[name] = kw
+            elif u < 0.25:                                         # deleted
+                px, po = both_pods(name, **old)
+                xe.unlist_pod("default", name); oc.unlist_pod("default", name)
+                xe.informer_delete(px); oc.informer_delete(po)
+                del state[name]
+            else:                                                  # updated
+                kw = dict(old)
+                if u < 0.6:
+                    kw.update(node=str(rng.choice(names)), annotations={O.IDX: str(int(rng.integers(-1, 5))), O.POD: str(int(rng.choice([512, 2048])))})
+                elif u < 0.8:
+                    kw["phase"] = int(rng.choice([X.RUNNING, X.SUCCEEDED, X.FAILED]))
+                else:
+                    kw["deleting"] = True
+                ox, oo = both_pods(name, **old)
+                nx, no = both_pods(name, **kw)
+                xe.list_pod(nx); oc.list_pod(no)
+                xe.informer_update(ox, nx); oc.informer_update(oo, no)
+                state[name] = kw
+            assert xe.queue_len == oc.queue_len
+            if step % 7 == 0:
+                assert xe.drain() == oc.drain()
+                check_state(xe, oc, names)
+                for kw in state.values():
+                    assert xe.known_pod(kw["uid"]) == oc.known_pod(kw["uid"])
+        assert xe.drain() == oc.drain()
+        check_state(xe, oc, names)
