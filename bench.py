@@ -220,7 +220,7 @@ def run_product(args):
     words = (N + 31) // 32
     stride = (words + 31) // 32 * 32  # 128-byte rows
 
-    snap = gsx.Snapshot(N, sc.max_devs, sc.n_pods + P, device=local_rank)
+    snap = gsx.Snapshot(N, sc.max_devs, sc.n_pods + P + 8192, device=local_rank)
     snap.node_upsert(sc.gs_nodes())
     snap.pods_load(sc.gs_pod_records())
     snap.rebuild()
@@ -328,6 +328,54 @@ def run_product(args):
         extra["rebuild_gbs"] = (sc.n_pods * 16 + N * sc.max_devs * 8) / (extra["rebuild_ms"] * 1e-3) / 1e9 if rb[0] else None
     except Exception as ex:  # report, do not hide
         extra["bind_error"] = repr(ex)
+
+    # config 5 (churn replay): batches of 1000 pod events (55 % add, 45 % delete of a live slot) interleaved with
+    # a Filter of 1000 pods + 200 Binds every fifth batch, back to back through the host-buffer C-ABI calls
+    try:
+        rngc = np.random.default_rng(0xC5)
+        free_slot0 = sc.n_pods + 4096
+        n_churn_slots = min(P, 4096)
+        live = np.zeros(n_churn_slots, dtype=bool)
+        batches = []
+        for _ in range(50):
+            ev = np.zeros(1000, dtype=synth.EVENT_DT)
+            is_add = rngc.random(1000) < 0.55
+            slots = rngc.integers(0, n_churn_slots, 1000)
+            is_add |= ~live[slots]
+            ev["slot"] = free_slot0 + slots
+            ev["op"] = (~is_add).astype(np.uint8)
+            ev["node_idx"] = rngc.integers(0, N, 1000)
+            ev["dev"] = rngc.integers(0, sc.max_devs, 1000)
+            ev["mem"] = rngc.choice(synth.CATALOGUE[:6], 1000)
+            ev["counted"] = 1
+            live[slots] = is_add
+            batches.append(ev)
+        creq = synth.make_requests(1000, REQ_KIND, 0xC5).astype(np.uint64)
+        cout = np.empty((1000, stride), dtype=np.uint32)
+        cb_nodes = rngc.integers(0, N, 200)
+        snap.profile(True)
+        snap.profile_reset()
+        t0 = time.perf_counter()
+        n_ev = n_f = n_b = 0
+        for k, ev in enumerate(batches):
+            snap.pods_apply(ev)
+            n_ev += len(ev)
+            if k % 5 == 4:
+                snap.filter_batch(creq, stride, out=cout)
+                got = snap.bind_batch(synth.bind_records(cb_nodes, creq[:200].view(np.int64), first_slot=sc.n_pods + 2048))
+                snap.bind_rollback(np.arange(200, dtype=np.uint32)[got >= 0] + sc.n_pods + 2048)
+                n_f += 1
+                n_b += 200
+        wall = time.perf_counter() - t0
+        pr = snap.profile_read()
+        snap.profile(False)
+        extra["churn"] = {"events": n_ev, "filters_of_1000": n_f, "binds": n_b, "wall_s": wall,
+                          "events_per_sec_e2e": n_ev / wall,
+                          "apply_device_us_per_1000_events": 1e3 * pr["apply"][1] / max(1, pr["apply"][0] // 2),
+                          "note": "wall time includes the profiling synchronisation after every kernel"}
+        snap.pods_apply(synth.remove_events(free_slot0 + np.arange(n_churn_slots)))
+    except Exception as ex:
+        extra["churn_error"] = repr(ex)
 
     # end to end through the host-buffer C-ABI call: pinned request in, pinned bitmap out, every step
     h_req = gsx.PinnedBuffer(P, np.uint64)
