@@ -224,6 +224,9 @@ def run_product(args):
     snap.node_upsert(sc.gs_nodes())
     snap.pods_load(sc.gs_pod_records())
     snap.rebuild()
+    # consecutive batches may overlap on the GPU (prep of batch k+1 under the tail of expand of batch k); the
+    # request array is resident before the first step and the four outputs rotate, as the option requires
+    snap.set_option(gsx.capi.OPT_PIPELINE_FILTERS, 1)
 
     dev = torch.device("cuda", local_rank)
     d_req = torch.from_numpy(reqs.view(np.int64)).to(dev)
@@ -433,6 +436,7 @@ def run_product(args):
             "config": {"workload": WORKLOAD, "nodes_per_gpu": N, "devices_per_node": sc.max_devs, "running_pods_per_gpu": sc.n_pods,
                        "pending_pods": P, "requests": REQ_KIND, "bitmap_row_stride_words": stride,
                        "l2": f"{N_OUT_BUFFERS} rotating output buffers of {P * stride * 4 / 1e6:.1f} MB (> 126 MB L2 in total)",
+                       "pipelining": "GS_OPT_PIPELINE_FILTERS: the prep kernel of step k+1 may run under the tail of step k's expand kernel",
                        "parallelism": f"nodes sharded over {world} GPU(s), weak scaling, no data-path collective"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(gpu_launches),
             "kernel_ms": kernel_ms, "clocks": clocks,

@@ -19,6 +19,7 @@ POD_VALID, POD_COUNTED = 1, 2
 BIND_NO_DEVICE, BIND_NODE_NOT_FOUND = -1, -2
 MAX_DEVS, MAX_BATCH = 64, 12288
 STAGE_SORT, STAGE_NODE_RANK, STAGE_EXPAND = 1, 2, 4
+OPT_PIPELINE_FILTERS = 1
 K_REBUILD, K_APPLY, K_SORT, K_NODE_RANK, K_EXPAND, K_BIND_SORT, K_BIND_SCAN = range(7)
 KERNEL_NAMES = ["rebuild", "apply", "sort", "node_rank", "expand", "bind_sort", "bind_scan"]
 
@@ -37,7 +38,7 @@ EXPORTS = [
     "gs_node_upsert", "gs_node_count", "gs_pods_load", "gs_rebuild", "gs_pods_apply", "gs_filter_batch",
     "gs_filter_batch_device", "gs_filter_stages_device", "gs_node_classes", "gs_bind_batch", "gs_bind_rollback", "gs_inspect",
     "gs_read_used", "gs_read_pods", "gs_host_alloc", "gs_host_free", "gs_profile_enable", "gs_profile_read",
-    "gs_profile_reset", "gs_launch_count", "gs_device_ptrs", "gs_pods_apply_static",
+    "gs_profile_reset", "gs_launch_count", "gs_device_ptrs", "gs_pods_apply_static", "gs_set_option",
 ]
 
 
@@ -94,6 +95,7 @@ def load():
         "gs_launch_count": (C.c_int, [vp, u64p]),
         "gs_device_ptrs": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
         "gs_pods_apply_static": (C.c_int, [C.c_int, vp, u32, vp, u32, vp, u32, u32, vp, vp]),
+        "gs_set_option": (C.c_int, [vp, C.c_int, C.c_int]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -253,6 +255,9 @@ class Snapshot:
         out = np.empty(n, dtype=POD_DT)
         _check(load().gs_read_pods(self.h, first_slot, n, _ptr(out)))
         return out
+
+    def set_option(self, option: int, value: int):
+        _check(load().gs_set_option(self.h, option, value))
 
     # ---- profiling ----
     def profile(self, on: bool):

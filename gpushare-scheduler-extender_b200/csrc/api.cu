@@ -40,7 +40,10 @@ namespace {
 struct Guard {
     gs_snapshot* s;
     std::unique_lock<std::mutex> lk;
-    explicit Guard(gs_snapshot* s_) : s(s_), lk(s_->mu) {}
+    // every entry point except the filters breaks a chain of back-to-back filters (see filter_chunk)
+    explicit Guard(gs_snapshot* s_, bool is_filter = false) : s(s_), lk(s_->mu) {
+        if (!is_filter) s->prev_filter = false;
+    }
 };
 
 int use_device(gs_snapshot* s) {
@@ -145,14 +148,23 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     if (n_pods == 0 || words == 0) return GS_OK;
     const uint32_t words_pad = (words + gs::kTileWords - 1) / gs::kTileWords * gs::kTileWords;
     if (words_pad > s->rank_words) return fail(GS_ERR_CAPACITY, "rank planes too small");
+    const uint32_t set = s->fb_set;
+    if (stages == 7u) s->fb_set ^= 1u;  // full launches alternate; single-stage profiling launches stay on one set
     gs::FilterBuffers fb;
-    fb.grouped_req = s->d_sorted_keys;
-    fb.perm = s->d_perm;
-    fb.row_bucket = s->d_row_bucket;
+    fb.grouped_req = s->d_sorted_keys + (size_t)set * GS_MAX_BATCH;
+    fb.perm = s->d_perm + (size_t)set * GS_MAX_BATCH;
+    fb.row_bucket = s->d_row_bucket + (size_t)set * GS_MAX_BATCH;
     fb.pod_hist = s->d_pod_hist;
-    fb.planes = s->d_rank_planes;
-    fb.node_key = s->d_node_key;
-    fb.sched = s->d_sched;
+    fb.planes = s->d_rank_planes + (size_t)set * s->rank_words * gs::kRankPlanes;
+    fb.node_key = s->d_node_key + (size_t)set * s->rank_words * 32;
+    fb.sched = s->d_sched + set * 2;
+    // With GS_OPT_PIPELINE_FILTERS, a filter that directly follows another filter of this snapshot on the same
+    // stream, writing somewhere else, does not wait for that filter's expand kernel to drain before its own prep
+    // kernel starts (the two touch different work-buffer sets).  Anything else keeps plain stream order.
+    const char* out_lo = reinterpret_cast<const char*>(d_out);
+    const char* out_hi = out_lo + (size_t)n_pods * row_stride * sizeof(uint32_t);
+    const bool overlap_ok = s->pipeline && stages == 7u && s->prev_filter && s->prev_stream == st &&
+                            (out_hi <= s->prev_out_lo || out_lo >= s->prev_out_hi);
     // bucket scale: requests up to the largest device capacity spread over all 512 buckets
     uint32_t bits = 0;
     while (bits < 64 && (s->max_capacity >> bits) != 0) ++bits;
@@ -162,12 +174,16 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     if (do_pods || do_nodes)
         rc = timed(s, do_pods ? GS_K_SORT : GS_K_NODE_RANK, st, 1, [&] {
             return gs::launch_prep(d_req, n_pods, do_pods, do_nodes, shift, fb, s->d_used, s->d_cap, s->d_nodeinfo,
-                                   s->n_nodes, s->max_devs, words_pad, st);
+                                   s->n_nodes, s->max_devs, words_pad, overlap_ok, st);
         });
     if (rc) return rc;
     if (stages & GS_STAGE_EXPAND)
         rc = timed(s, GS_K_EXPAND, st, 1,
                    [&] { return gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, st); });
+    s->prev_filter = rc == GS_OK && stages == 7u && !s->profiling;
+    s->prev_stream = st;
+    s->prev_out_lo = out_lo;
+    s->prev_out_hi = out_hi;
     return rc;
 }
 
@@ -239,19 +255,19 @@ int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32
     CU_NEW(cudaMalloc(&s->d_nodeinfo, (size_t)max_nodes * sizeof(uint32_t)));
     CU_NEW(cudaMalloc(&s->d_pods, (size_t)max_pods * sizeof(gs_pod_record)));
     CU_NEW(cudaMalloc(&s->d_last_ev, (size_t)max_pods * sizeof(int32_t)));
-    CU_NEW(cudaMalloc(&s->d_sorted_keys, (size_t)GS_MAX_BATCH * sizeof(u64)));
-    CU_NEW(cudaMalloc(&s->d_perm, (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
-    CU_NEW(cudaMalloc(&s->d_rank_planes, (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t)));
-    CU_NEW(cudaMalloc(&s->d_node_key, (size_t)s->rank_words * 32 * sizeof(u64)));
-    CU_NEW(cudaMalloc(&s->d_row_bucket, (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
+    CU_NEW(cudaMalloc(&s->d_sorted_keys, 2 * (size_t)GS_MAX_BATCH * sizeof(u64)));
+    CU_NEW(cudaMalloc(&s->d_perm, 2 * (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
+    CU_NEW(cudaMalloc(&s->d_rank_planes, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t)));
+    CU_NEW(cudaMalloc(&s->d_node_key, 2 * (size_t)s->rank_words * 32 * sizeof(u64)));
+    CU_NEW(cudaMalloc(&s->d_row_bucket, 2 * (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
     CU_NEW(cudaMalloc(&s->d_pod_hist, 516 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 516 * sizeof(uint32_t), s->stream));
-    CU_NEW(cudaMalloc(&s->d_sched, 2 * sizeof(uint32_t)));
-    CU_NEW(cudaMemsetAsync(s->d_sched, 0, 2 * sizeof(uint32_t), s->stream));
+    CU_NEW(cudaMalloc(&s->d_sched, 4 * sizeof(uint32_t)));
+    CU_NEW(cudaMemsetAsync(s->d_sched, 0, 4 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_used, 0, (size_t)max_nodes * max_devs * sizeof(u64), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_cap, 0, (size_t)max_nodes * sizeof(u64), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_pods, 0, (size_t)max_pods * sizeof(gs_pod_record), s->stream));
-    CU_NEW(cudaMemsetAsync(s->d_rank_planes, 0, (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t), s->stream));
+    CU_NEW(cudaMemsetAsync(s->d_rank_planes, 0, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t), s->stream));
     CU_NEW(gs::launch_fill_i32(s->d_last_ev, -1, max_pods, s->stream));
     CU_NEW(gs::launch_fill_i32(reinterpret_cast<int32_t*>(s->d_nodeinfo), (int32_t)gs::kUnsetNodeinfo, max_nodes, s->stream));
     CU_NEW(cudaStreamSynchronize(s->stream));
@@ -405,7 +421,7 @@ int gs_pods_apply(gs_snapshot* s, const gs_pod_event* events, uint32_t n) {
 int gs_filter_batch_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods, uint32_t* d_out_bitmap,
                            uint32_t row_stride_words, void* cuda_stream) {
     if (!s || ((!d_req || !d_out_bitmap) && n_pods)) return fail(GS_ERR_INVALID, "null argument");
-    Guard g(s);
+    Guard g(s, true);
     int rc = use_device(s);
     if (rc) return rc;
     cudaStream_t st = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : s->stream;
@@ -416,7 +432,7 @@ int gs_filter_stages_device(gs_snapshot* s, uint32_t stage_mask, const uint64_t*
                             uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream) {
     if (!s || !d_req || !d_out_bitmap) return fail(GS_ERR_INVALID, "null argument");
     if (n_pods > GS_MAX_BATCH) return fail(GS_ERR_INVALID, "n_pods > GS_MAX_BATCH");
-    Guard g(s);
+    Guard g(s, true);
     int rc = use_device(s);
     if (rc) return rc;
     if (row_stride_words < bitmap_words(s)) return fail(GS_ERR_INVALID, "row_stride_words too small");
@@ -427,7 +443,7 @@ int gs_filter_stages_device(gs_snapshot* s, uint32_t stage_mask, const uint64_t*
 int gs_filter_batch(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint32_t* out_bitmap,
                     uint32_t row_stride_words) {
     if (!s || ((!req || !out_bitmap) && n_pods)) return fail(GS_ERR_INVALID, "null argument");
-    Guard g(s);
+    Guard g(s, true);
     int rc = use_device(s);
     if (rc) return rc;
     if (n_pods == 0) return GS_OK;
@@ -564,6 +580,17 @@ int gs_host_free(void* p) {
     if (!p) return GS_OK;
     CU(cudaFreeHost(p));
     return GS_OK;
+}
+
+int gs_set_option(gs_snapshot* s, int option, int value) {
+    if (!s) return fail(GS_ERR_INVALID, "null snapshot");
+    Guard g(s);
+    if (option == GS_OPT_PIPELINE_FILTERS) {
+        s->pipeline = value != 0;
+        s->prev_filter = false;
+        return GS_OK;
+    }
+    return fail(GS_ERR_INVALID, "unknown option %d", option);
 }
 
 int gs_profile_enable(gs_snapshot* s, int on) {

@@ -55,6 +55,15 @@ struct gs_snapshot {
     uint32_t* d_rank_planes = nullptr;        // [rank_words / kTileWords][kRankPlanes][kTileWords] (K3)
     unsigned long long* d_node_key = nullptr; // [rank_words * 32] (K3)
     uint32_t* d_sched = nullptr;              // [2] tile scheduler of k_expand (self re-arming)
+    // The K3 work buffers above exist twice (set 0 / set 1, second copy right behind the first) and filter
+    // launches alternate between them, so that with GS_OPT_PIPELINE_FILTERS the prep kernel of one batch can run
+    // under the tail of the previous batch's expand kernel.
+    uint32_t fb_set = 0;
+    bool pipeline = false;            // GS_OPT_PIPELINE_FILTERS
+    bool prev_filter = false;         // the last operation enqueued for this snapshot was a filter ...
+    cudaStream_t prev_stream = nullptr;  // ... on this stream ...
+    const char* prev_out_lo = nullptr;   // ... writing [prev_out_lo, prev_out_hi)
+    const char* prev_out_hi = nullptr;
     uint32_t rank_words = 0;
     void* d_stage = nullptr;                  // generic device staging (events, binds, reqs, out)
     size_t d_stage_bytes = 0;

@@ -231,10 +231,14 @@ template <int kDevStride>
 __global__ void __launch_bounds__(kPrepThreads)
 k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32_t shift, FilterBuffers fb,
        const u64* __restrict__ used, const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
-       uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words) {
+       uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, uint32_t overlap_previous) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // programmatic dependent launch: k_expand may start its prologue now; it waits (griddepcontrol.wait)
-    // for this grid to complete before it reads anything written here
+    // Programmatic dependent launch, both ways.  This grid is launched as a programmatic dependent of whatever
+    // precedes it in the stream: normally it waits for that work to complete and flush; only when the host knows
+    // the predecessor is the expand kernel of another filter batch that shares nothing with this one does it run
+    // under that kernel's tail.  And k_expand may start its prologue now; it waits (griddepcontrol.wait) for
+    // this grid to complete before it reads anything written here.
+    if (!overlap_previous) asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (blockIdx.x < pod_blocks) {
         // ---------------- pod role ----------------
@@ -462,8 +466,10 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         sm.n_partial = 0;
         sm.n_dense = 0;
     }
-    // everything above overlapped the tail of k_prep; its results are needed from here on
+    // everything above overlapped the tail of k_prep; its results are needed from here on.  After the wait,
+    // everything that precedes this grid in the stream is complete, so a following grid may be let in.
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (tid == 0) request(blockIdx.x, 0);
     __syncthreads();
     uint32_t cur = blockIdx.x;
@@ -760,17 +766,27 @@ cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n
 
 cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do_nodes, uint32_t shift,
                         const FilterBuffers& fb, const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo,
-                        uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, cudaStream_t st) {
+                        uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, bool overlap_previous,
+                        cudaStream_t st) {
     const uint32_t pod_blocks = do_pods ? (n_pods + kPrepThreads - 1) / kPrepThreads : 0u;
     const uint32_t node_blocks = do_nodes ? (n_words + kPrepThreads / 32 - 1) / (kPrepThreads / 32) : 0u;
     if (pod_blocks + node_blocks == 0) return cudaSuccess;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(pod_blocks + node_blocks);
+    cfg.blockDim = dim3(kPrepThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const uint32_t ov = overlap_previous ? 1u : 0u;
     if (dev_stride == 8)
-        k_prep<8><<<pod_blocks + node_blocks, kPrepThreads, 0, st>>>(d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap,
-                                                                     d_nodeinfo, n_nodes, dev_stride, n_words);
-    else
-        k_prep<0><<<pod_blocks + node_blocks, kPrepThreads, 0, st>>>(d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap,
-                                                                     d_nodeinfo, n_nodes, dev_stride, n_words);
-    return cudaGetLastError();
+        return cudaLaunchKernelEx(&cfg, k_prep<8>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
+                                  dev_stride, n_words, ov);
+    return cudaLaunchKernelEx(&cfg, k_prep<0>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
+                              dev_stride, n_words, ov);
 }
 
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,

@@ -25,7 +25,7 @@ cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n
 cudaError_t launch_prep(const unsigned long long* d_req, uint32_t n_pods, bool do_pods, bool do_nodes, uint32_t shift,
                         const FilterBuffers& fb, const unsigned long long* d_used, const unsigned long long* d_cap,
                         const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words,
-                        cudaStream_t st);
+                        bool overlap_previous, cudaStream_t st);
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
                           uint32_t row_stride, uint32_t* d_out, cudaStream_t st);
 

@@ -199,6 +199,15 @@ int gs_read_pods(gs_snapshot* s, uint32_t first_slot, uint32_t n, gs_pod_record*
 int gs_host_alloc(size_t bytes, void** out);
 int gs_host_free(void* p);
 
+/* Options.  GS_OPT_PIPELINE_FILTERS (default 0): consecutive gs_filter_batch_device calls on one stream may
+ * overlap on the GPU -- the second call's preparation kernel runs under the tail of the first call's bitmap
+ * kernel (they use separate work buffers).  Contract when set: the request array of a call must already be
+ * complete when the PREVIOUS filter call was enqueued (do not produce it with a kernel enqueued in between; a
+ * cudaMemcpyAsync in between is fine, it restores plain stream order), and a call whose output overlaps the
+ * previous call's output is not overlapped.  Results are identical either way. */
+enum { GS_OPT_PIPELINE_FILTERS = 1 };
+int gs_set_option(gs_snapshot* s, int option, int value);
+
 /* Device-time profiling of the library's own kernels (off by default). */
 int gs_profile_enable(gs_snapshot* s, int on);
 int gs_profile_read(gs_snapshot* s, int kernel_id, uint64_t* out_launches, double* out_total_ms);

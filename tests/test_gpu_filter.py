@@ -159,3 +159,41 @@ def test_full_size_configs(cfg, kind):
         zero = np.flatnonzero(reqs == 0)
         if len(zero):
             assert (got[zero[0]] == S.pack_bitmap(elig[None, :], stride)[0]).all()
+
+
+def test_pipelined_back_to_back_filters_are_identical():
+    """GS_OPT_PIPELINE_FILTERS lets the preparation kernel of one batch run under the tail of the previous batch's
+    bitmap kernel.  Twelve different batches are enqueued back to back (no host synchronisation in between) into
+    rotating output buffers, plus one call that reuses the previous output (which must fall back to stream order);
+    every bitmap must equal the reference."""
+    import torch
+
+    sc = synth.make_config("C3")
+    cap, used, ndev, cls, _ = H.soa_state(sc)
+    key, elig = S.node_keys(cap, used, ndev, cls)
+    P = 3000
+    with H.load_snapshot(sc) as s:
+        s.set_option(gsx.capi.OPT_PIPELINE_FILTERS, 1)
+        stride = (s.bitmap_words + 3) // 4 * 4
+        st = torch.cuda.Stream()
+        batches = [synth.make_requests(P, "adversarial" if i % 2 else "catalogue", 100 + i).astype(np.uint64) for i in range(12)]
+        d_reqs = [torch.from_numpy(b.view(np.int64)).cuda() for b in batches]
+        outs = [torch.zeros((P, stride), dtype=torch.int32, device="cuda") for _ in range(3)]
+        torch.cuda.synchronize()
+        got = []
+        for i, d_req in enumerate(d_reqs):
+            o = outs[i % 3] if i != 7 else outs[(i - 1) % 3]        # call 7 overwrites call 6's buffer
+            s.filter_batch_device(d_req.data_ptr(), P, o.data_ptr(), stride, st.cuda_stream)
+            if i % 3 == 2 or i in (6, 7):                            # read back before the buffer is reused
+                st.synchronize()
+                for j in ([i] if i in (6, 7) else [i - 2, i - 1, i]):
+                    if j not in (6, 7) or j == i:
+                        src = o if j == i else outs[j % 3]
+                        got.append((j, src.cpu().numpy().view(np.uint32).copy()))
+        st.synchronize()
+        seen = set()
+        for j, bm in got:
+            want = S.pack_bitmap(S.filter_pass(batches[j], key, elig), stride)
+            assert (bm == want).all(), j
+            seen.add(j)
+        assert seen == set(range(12))
