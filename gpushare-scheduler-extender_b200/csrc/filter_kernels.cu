@@ -215,7 +215,7 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
 // so that for a closed bucket b'  q' > b' implies key >= every request in it and q' < b' implies
 // key < all of them.  q' is written bit-sliced, plane-major inside blocks of kTileWords words:
 //   planes[((word / kTileWords) * kRankPlanes + k) * kTileWords + word % kTileWords] = bit k of 32 q'.
-constexpr int kPrepThreads = 512;
+constexpr int kPrepThreads = 128;  // small blocks: they fit next to a fully resident k_expand of the previous batch
 constexpr uint32_t kBuckets = 512;
 
 __device__ __forceinline__ u64 node_key_generic(const u64* __restrict__ used_row, u64 cap, uint32_t ndev) {
@@ -245,7 +245,8 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         __shared__ uint32_t base[kBuckets];
         __shared__ uint32_t wsum[kPrepThreads / 32];
         __shared__ bool is_last;
-        static_assert(kPrepThreads == (int)kBuckets, "one bucket per thread in the scan");
+        constexpr int kPer = kBuckets / kPrepThreads;  // buckets scanned per thread
+        static_assert(kPer == 4, "the scan below reads four counts per thread");
         uint32_t* ghist = fb.pod_hist;  // [kBuckets] counts, [kBuckets] arrived blocks, [kBuckets + 1] finished blocks
         const uint32_t i = blockIdx.x * kPrepThreads + tid;
         uint32_t sl = 0;
@@ -256,8 +257,8 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
             const uint32_t b = bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1;
             sl = (b << 16) | atomicAdd(&ghist[b], 1u);  // arrival number inside the bucket
         }
-        // barrier among the pod blocks (they are the first blocks of a grid far smaller than the GPU, so
-        // all of them are resident): the bucket counts are complete once every block has arrived
+        // barrier among the pod blocks (the first blocks of a small grid of small blocks: all of them become
+        // resident, even next to another kernel): the bucket counts are complete once every block has arrived
         __syncthreads();
         if (tid == 0) {
             __threadfence();
@@ -268,8 +269,9 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         }
         __syncthreads();
         // bucket counts -> offsets (every block scans the 512 counts itself), then the block's own pods
-        const uint32_t cnt = __ldcg(&ghist[tid]);
-        uint32_t incl = cnt;
+        const uint4 c4 = __ldcg(reinterpret_cast<const uint4*>(ghist) + tid);
+        const uint32_t sum = c4.x + c4.y + c4.z + c4.w;
+        uint32_t incl = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
@@ -277,18 +279,12 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         }
         if (lane == 31) wsum[warp] = incl;
         __syncthreads();
-        if (warp == 0) {
-            const uint32_t w = lane < kPrepThreads / 32 ? wsum[lane] : 0u;
-            uint32_t wi = w;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
-                if ((int)lane >= o) wi += t;
-            }
-            if (lane < kPrepThreads / 32) wsum[lane] = wi - w;
-        }
-        __syncthreads();
-        base[tid] = wsum[warp] + incl - cnt;
+        uint32_t run = incl - sum;
+        for (uint32_t w = 0; w < warp; ++w) run += wsum[w];
+        base[tid * 4 + 0] = run;
+        base[tid * 4 + 1] = run + c4.x;
+        base[tid * 4 + 2] = run + c4.x + c4.y;
+        base[tid * 4 + 3] = run + c4.x + c4.y + c4.z;
         __syncthreads();
         if (i < n_pods) {
             const uint32_t b = sl >> 16;
@@ -301,7 +297,7 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         if (tid == 0) is_last = atomicAdd(&ghist[kBuckets + 1], 1u) == pod_blocks - 1;
         __syncthreads();
         if (is_last) {
-            ghist[tid] = 0;
+            reinterpret_cast<uint4*>(ghist)[tid] = make_uint4(0, 0, 0, 0);
             if (tid < 2) ghist[kBuckets + tid] = 0;
         }
         return;
