@@ -157,6 +157,7 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     fb.pod_hist = s->d_pod_hist;
     fb.planes = s->d_rank_planes + (size_t)set * s->rank_words * gs::kRankPlanes;
     fb.node_key = s->d_node_key + (size_t)set * s->rank_words * 32;
+    fb.node_key32 = s->d_node_key32 + (size_t)set * s->rank_words * 32;
     fb.sched = s->d_sched + set * 2;
     // With GS_OPT_PIPELINE_FILTERS, a filter that directly follows another filter of this snapshot on the same
     // stream, writing somewhere else, does not wait for that filter's expand kernel to drain before its own prep
@@ -259,6 +260,7 @@ int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32
     CU_NEW(cudaMalloc(&s->d_perm, 2 * (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
     CU_NEW(cudaMalloc(&s->d_rank_planes, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t)));
     CU_NEW(cudaMalloc(&s->d_node_key, 2 * (size_t)s->rank_words * 32 * sizeof(u64)));
+    CU_NEW(cudaMalloc(&s->d_node_key32, 2 * (size_t)s->rank_words * 32 * sizeof(uint32_t)));
     CU_NEW(cudaMalloc(&s->d_row_bucket, 2 * (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
     CU_NEW(cudaMalloc(&s->d_pod_hist, 516 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 516 * sizeof(uint32_t), s->stream));
@@ -290,6 +292,7 @@ int gs_snapshot_destroy(gs_snapshot* s) {
     cudaFree(s->d_perm);
     cudaFree(s->d_rank_planes);
     cudaFree(s->d_node_key);
+    cudaFree(s->d_node_key32);
     cudaFree(s->d_row_bucket);
     cudaFree(s->d_pod_hist);
     cudaFree(s->d_sched);

@@ -54,6 +54,7 @@ struct gs_snapshot {
     unsigned long long max_capacity = 0;      // largest dev_capacity of an OK node ever upserted (bucket scale)
     uint32_t* d_rank_planes = nullptr;        // [rank_words / kTileWords][kRankPlanes][kTileWords] (K3)
     unsigned long long* d_node_key = nullptr; // [rank_words * 32] (K3)
+    uint32_t* d_node_key32 = nullptr;         // [rank_words * 32] (K3)
     uint32_t* d_sched = nullptr;              // [2] tile scheduler of k_expand (self re-arming)
     // The K3 work buffers above exist twice (set 0 / set 1, second copy right behind the first) and filter
     // launches alternate between them, so that with GS_OPT_PIPELINE_FILTERS the prep kernel of one batch can run

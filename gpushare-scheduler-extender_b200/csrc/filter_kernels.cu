@@ -6,13 +6,13 @@
 // request every node's column is a step: ones up to the last request <= key[n], zeros after.  An exact
 // sort is not needed: it is enough to group the pods into narrow value buckets and settle the nodes
 // whose key falls inside a tile's own bucket range by direct comparison with each row's
-// request.  Three kernels:
-//   k_bucket_pods : one CTA groups the (<= GS_MAX_BATCH) requests into <= 512 value buckets.
-//   k_node_bucket : per node, key = max available over its devices and the bucket the key falls in,
-//                   bucket ids written bit-sliced (10 planes per 32-node word).
-//   k_expand      : writes the [P][N/32] bitmap tile by tile.  One thread turns the bucket ids of 32
-//                   nodes into a word with 10 LOP3s; only nodes whose bucket lies inside the tile's own
-//                   bucket range need the exact 64-bit comparison.
+// request.  Two kernels:
+//   k_prep   : pod blocks group the (<= GS_MAX_BATCH) requests into <= 512 value buckets; node blocks compute,
+//              per node, key = max available over its devices and the bucket the key falls in, bucket ids
+//              written bit-sliced (10 planes per 32-node word).
+//   k_expand : writes the [P][N/32] bitmap tile by tile.  One thread turns the bucket ids of 32 nodes into
+//              a word with 10 LOP3s; only nodes whose bucket lies inside the tile's own bucket range need
+//              the exact comparison.
 // (k_radix_sort, a stable single-CTA LSD radix sort, orders the bind queue by node for K4.)
 #include "common.cuh"
 #include "kernels.h"
@@ -330,6 +330,7 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         }
     }
     fb.node_key[node] = key;
+    fb.node_key32[node] = key > 0xffffffffull ? 0xffffffffu : (uint32_t)key;  // exact against any request below 2^32
     uint32_t mine = 0;
 #pragma unroll
     for (int k = 0; k < kRankPlanes; ++k) {
@@ -353,35 +354,50 @@ __device__ __forceinline__ uint32_t planes_ge(const uint32_t (&a)[kRankPlanes], 
 
 // A tile is kTileRows consecutive grouped pods x kTileWords words (4096 nodes); its rows span request
 // buckets [bmin, bmax].  A node with q' > bmax passes in every row (base word), one with q' < bmin in
-// none; only nodes with bmin <= q' <= bmax need the exact 64-bit comparison key >= req per row.  Words
-// holding such nodes are recomputed row by row (a few such nodes: lane = row, exact compares; many:
-// lane = node, a binary search over the tile's sorted requests) into a small shared-memory patch;
-// every other word goes from registers straight to global memory.  Stores are 16 bytes per lane, 512
+// none; only nodes with bmin <= q' <= bmax need the exact comparison key >= req per row.  Words holding
+// such nodes ("partial" words) are settled per tile in one of two ways:
+//   sparse tile (<= kSparseCap partial words, each with <= kSparseMax compared nodes): lane = row, exact
+//     compares against the few keys, results in a small shared-memory patch;
+//   dense tile (anything else): the tile's rows are sorted, every node of a partial word gets
+//     cnt = #{rows : req <= key} by binary search (lane = node), and row i of the sorted tile has the
+//     node's bit set iff cnt > i; the counts are kept bit-sliced.
+// Every other word goes from registers straight to global memory.  Stores are 16 bytes per lane, 512
 // contiguous bytes per warp and row.  (Bulk asynchronous stores of 512-byte row segments from a
 // shared-memory tile were measured slower than this: profiles/NOTES.md.)
-constexpr int kSparseMax = 4;           // up to this many compared nodes a word takes the lane = row path
-constexpr uint32_t kPatchWords = 4096;  // patch capacity in 32-bit words (rows x patched words per sub-pass)
+//
+// Node keys reach shared memory only through bulk asynchronous copies: an ordinary load issued by an SM
+// that is streaming stores waits behind them for microseconds (profiles/NOTES.md), and so does everything
+// that depends on it.  The copies are issued as soon as the tile is classified, and the lanes whose four
+// words are the same in every row store all their rows while the keys are in flight.
+//
+// Keys are compared as 32-bit saturated values (node_key32 = min(key, 2^32 - 1)), which is exact for every
+// request below 2^32; a tile holding a larger request (a wrapped negative sum, pkg/cache/nodeinfo.go:217)
+// is a "wide" tile and takes the dense path over the full 64-bit keys, half a tile of keys at a time.
+constexpr int kSparseMax = 4;       // compared nodes per word on the lane = row path
+constexpr uint32_t kSparseCap = 16; // partial words per tile on that path
+constexpr uint32_t kPatchStride = kTileRows + 1;  // odd: phase D reads one row of several patched words
+constexpr uint32_t kStageWords = 4096;            // 16 KB: the tile's 4096 32-bit keys, or 2048 64-bit ones
 
 struct ExpandSmem {
-    uint32_t patch[kPatchWords];        // per-row values of the words that differ from row to row
+    // dense tile: node keys; sparse tile: [kSparseCap][32] keys, then [kSparseCap][kPatchStride] patch
+    uint32_t stage[kStageWords];
     u64 req[kTileRows];                 // requests of the tile's rows (~0 beyond the last row)
-    u64 req_sorted[kTileRows];          // the same in ascending order (only when a dense word needs it)
-    u64 ekey[kTileWords * kSparseMax];  // keys of the compared nodes of sparse words
+    u64 req_sorted[kTileRows];          // the same in ascending order (dense tiles)
     u64 off_sorted[kTileRows];
-    uint32_t ebits[kTileWords];         // their bit positions, 8 bits each (0xff = unused)
+    u64 row_off[kTileRows];             // word offset of every tile row's output row (pod index x row stride)
     uint32_t basew[kTileWords];         // nodes passing in every row
     uint32_t somew[kTileWords];         // nodes that can pass in some row (q' >= bmin)
-    u64 row_off[kTileRows];             // word offset of every tile row's output row (pod index x row stride)
-    uint32_t cntp[kTileWords * 8];      // dense words: per-node pass counts (0..64), bit-sliced, 7 planes used
-    uint8_t plist[kTileWords];          // words that need per-row values
+    uint32_t pmask[kTileWords];         // nodes that need the comparison (some & ~base)
+    uint32_t cntp[kTileWords * 8];      // dense tiles: per-node pass counts (0..64), bit-sliced, 7 planes used
+    uint8_t plist[kTileWords];          // the partial words
     uint8_t pidx[kTileWords];           // position in plist, 0xff = the word is the same in every row
-    uint8_t dlist[kTileWords];          // the dense ones among them
-    uint32_t n_partial, n_dense, next_tile;
+    uint32_t n_partial, n_heavy, next_tile;
 };
+constexpr uint32_t kSparseKeyWords = kSparseCap * 32;
+static_assert(kSparseKeyWords + kSparseCap * kPatchStride <= kStageWords, "sparse keys + patch share the stage");
 
-// Inputs of one tile, brought in by bulk asynchronous copies (TMA) that complete on an mbarrier.  They
-// are requested kPrefetch tiles ahead: ordinary loads issued from a CTA that is streaming stores queue
-// up behind those stores and would stall every tile for microseconds.
+// Inputs of one tile, brought in by bulk asynchronous copies (TMA) that complete on an mbarrier, one tile
+// ahead.
 constexpr int kPrefetch = 2;
 struct __align__(128) TileInputs {
     uint32_t planes[kRankPlanes * kTileWords];  // bucket-id planes of the tile's 128 words
@@ -417,6 +433,21 @@ __device__ __forceinline__ void bulk_load(void* sdst, const void* gsrc, uint32_t
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// orders this thread's earlier generic-proxy accesses to shared memory before its later asynchronous copies
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+#ifdef GS_EXPAND_TRACE
+// development builds only: per CTA and tile, SM cycle stamps of the phases (tools/expand_trace.py)
+constexpr int kTraceTiles = 6, kTraceSlots = 12;
+__device__ unsigned long long g_trace[148 * 5 * kTraceTiles * kTraceSlots];
+#define GS_TRACE(slot) \
+    do { if (tid == 0 && it < kTraceTiles) g_trace[((size_t)blockIdx.x * kTraceTiles + it) * kTraceSlots + (slot)] = clock64(); } while (0)
+#define GS_TRACE_VAL(slot, v) \
+    do { if (tid == 0 && it < kTraceTiles) g_trace[((size_t)blockIdx.x * kTraceTiles + it) * kTraceSlots + (slot)] = (v); } while (0)
+#else
+#define GS_TRACE(slot) do {} while (0)
+#define GS_TRACE_VAL(slot, v) do {} while (0)
+#endif
 
 template <bool kVec>
 __global__ void __launch_bounds__(kExpandThreads, 5)
@@ -427,11 +458,10 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
     constexpr uint32_t kWarps = kExpandThreads / 32;
     static_assert(kExpandThreads >= kTileWords + kTileRows, "phase A: one thread per word, one per row");
     const uint32_t* __restrict__ planes = fb.planes;
-    const u64* __restrict__ node_key = fb.node_key;
 
     __shared__ TileInputs tin[kPrefetch];
     __shared__ __align__(8) uint64_t tin_bar[kPrefetch];
-    __shared__ __align__(8) uint64_t key_bar;  // completion of on-demand key loads for dense words
+    __shared__ __align__(8) uint64_t key_bar;  // completion of the key copies of the current tile
     uint32_t key_phase = 0;
 
     // thread 0: request the inputs of the tile with ticket `ticket_no` into stage `stage`
@@ -448,19 +478,18 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         bulk_load(in.bucket, fb.row_bucket + j0, sizeof(in.bucket), &tin_bar[stage]);
     };
 
-    // Tile schedule: the first tile of a CTA is blockIdx.x; every later one is a ticket taken late in
-    // the current tile (after its dense work, if any), so a CTA never holds more than one tile ahead and
+    // Tile schedule: the first tile of a CTA is blockIdx.x; every later one is a ticket taken during the
+    // current tile (after its dense work, if any), so a CTA never holds more than one tile ahead and
     // CTAs stuck in a dense tile simply take fewer.  (Tickets taken several tiles ahead hoard when there
     // are only ~3 tiles per CTA: profiles/NOTES.md.)
     uint32_t ticket = 0;  // thread 0
     if (tid == 0) {
 #pragma unroll
         for (int i = 0; i < kPrefetch; ++i) mbar_init(&tin_bar[i], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         mbar_init(&key_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         sm.n_partial = 0;
-        sm.n_dense = 0;
+        sm.n_heavy = 0;
     }
     // everything above overlapped the tail of k_prep; its results are needed from here on.  After the wait,
     // everything that precedes this grid in the stream is complete, so a following grid may be let in.
@@ -478,9 +507,13 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         const uint32_t rows = min((uint32_t)kTileRows, n_pods - j0);
         const uint32_t w0 = cb * kTileWords;
         const TileInputs& in = tin[stage];
+        GS_TRACE(0);
         mbar_wait(&tin_bar[stage], parity);
+        GS_TRACE(1);
 
         // A: one thread per word (threads 0..127), one per row (threads 128..191)
+        uint32_t my_pi = 0xffu;  // threads 0..127: position of the thread's word among the partial ones
+        int big_req = 0;         // threads 128..191: the row's request does not fit 32 bits
         if (tid < kTileWords) {
             uint32_t a[kRankPlanes];
 #pragma unroll
@@ -490,60 +523,63 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             const uint32_t t_all = bmax == kBuckets ? kBuckets + 2u : bmax + 1u;
             const uint32_t all_rows = planes_ge(a, t_all);
             const uint32_t some_rows = planes_ge(a, bmin);
+            const uint32_t pm = some_rows & ~all_rows;
             sm.basew[tid] = all_rows;
             sm.somew[tid] = some_rows;
-            uint32_t pm = some_rows & ~all_rows;
-            uint8_t pi = 0xff;  // 0xff: same word in every row, 0xfe: dense, else: index into the patch
+            sm.pmask[tid] = pm;
             if (pm) {
-                if (__popc(pm) <= kSparseMax) {
-                    pi = (uint8_t)atomicAdd(&sm.n_partial, 1u);
-                    sm.plist[pi] = (uint8_t)tid;
-                    const u64* keys = node_key + (size_t)(w0 + tid) * 32;
-                    uint32_t eb = 0xffffffffu;
-                    u64 kk[kSparseMax];
-#pragma unroll
-                    for (int i = 0; i < kSparseMax; ++i) {
-                        kk[i] = 0;
-                        if (pm) {
-                            const uint32_t bit = __ffs(pm) - 1;
-                            pm &= pm - 1;
-                            kk[i] = __ldg(keys + bit);
-                            eb = (eb & ~(0xffu << (8 * i))) | (bit << (8 * i));
-                        }
-                    }
-#pragma unroll
-                    for (int i = 0; i < kSparseMax; ++i) sm.ekey[tid * kSparseMax + i] = kk[i];
-                    sm.ebits[tid] = eb;
-                } else {
-                    pi = 0xfe;
-                    sm.dlist[atomicAdd(&sm.n_dense, 1u)] = (uint8_t)tid;
-                }
+                my_pi = atomicAdd(&sm.n_partial, 1u);
+                sm.plist[my_pi] = (uint8_t)tid;
+                if (__popc(pm) > kSparseMax) sm.n_heavy = 1u;
             }
-            sm.pidx[tid] = pi;
+            sm.pidx[tid] = (uint8_t)my_pi;
         } else if (tid < kTileWords + kTileRows) {
             const uint32_t r = tid - kTileWords;
             const uint32_t row = (uint32_t)in.perm[r];
+            const u64 rq = in.req[r];
             sm.row_off[r] = (u64)row * row_stride;
-            sm.req[r] = r < rows ? in.req[r] : ~0ull;
+            sm.req[r] = r < rows ? rq : ~0ull;
+            big_req = (r < rows && (rq >> 32) != 0) ? 1 : 0;
         }
-        __syncthreads();  // phase A results are visible; nobody reads this stage's inputs any more
+        // phase A results are visible; nobody reads this stage's inputs any more
+        const bool wide = __syncthreads_or(big_req) != 0;
 
         const uint32_t np = sm.n_partial;
-        const uint32_t nd = sm.n_dense;
-        const bool dense = nd != 0;
-        if (!dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);  // consumed just before phase D
+        const bool dense = np != 0 && (sm.n_heavy != 0 || np > kSparseCap || wide);
+        const bool sparse = np != 0 && !dense;
+        GS_TRACE(2);
+        GS_TRACE_VAL(8, (unsigned long long)np | ((unsigned long long)dense << 16) | ((unsigned long long)wide << 17) | ((unsigned long long)tile << 32));
+        {
+            unsigned long long gt;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
+            GS_TRACE_VAL(9, gt);
+        }
 
-        // Words with many compared nodes want the tile's rows in ascending request order: then a node's
-        // column is a prefix of ones and one binary search per node replaces a comparison per row.
-        u64* kstage = reinterpret_cast<u64*>(sm.patch);
-        // one bulk copy brings the keys of 64 consecutive words (16 KB) into the staging area
-        auto fetch_keys = [&](uint32_t half) {
+        // the keys this tile needs, on their way while the rows that do not need them are stored
+        u64* const stage64 = reinterpret_cast<u64*>(sm.stage);
+        if (dense) {
             if (tid == 0) {
-                mbar_expect_tx(&key_bar, 64u * 256u);
-                bulk_load(kstage, node_key + (size_t)(w0 + half * 64u) * 32, 64u * 256u, &key_bar);
+                fence_async_smem();
+                mbar_expect_tx(&key_bar, kStageWords * 4u);
+                if (wide)  // the keys of the first 64 words
+                    bulk_load(stage64, fb.node_key + (size_t)w0 * 32, kStageWords * 4u, &key_bar);
+                else
+                    bulk_load(sm.stage, fb.node_key32 + (size_t)w0 * 32, kStageWords * 4u, &key_bar);
             }
-        };
-        if (dense) fetch_keys(0);  // overlaps the sort below
+        } else if (sparse) {
+            // each partial word's thread fetches the 32 keys of its word (128 bytes); the expected byte count
+            // may be posted after some of the copies have already landed, which the barrier allows
+            if (tid == 0) mbar_expect_tx(&key_bar, np * 128u);
+            if (my_pi != 0xffu) {
+                fence_async_smem();
+                bulk_load(&sm.stage[my_pi * 32], fb.node_key32 + (size_t)(w0 + tid) * 32, 128u, &key_bar);
+            }
+        }
+
+        if (!dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);  // consumed just before the stores
+
+        // Dense tiles want the tile's rows in ascending request order: then a node's column is a prefix of
+        // ones and one binary search per node replaces a comparison per row.
         if (dense && tid < kTileRows) {
             const u64 mine = sm.req[tid];
             uint32_t rank = 0;
@@ -555,159 +591,192 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             sm.req_sorted[rank] = mine;
             sm.off_sorted[rank] = sm.row_off[tid];
         }
-        const u64* __restrict__ treq = dense ? sm.req_sorted : sm.req;
-        const u64* __restrict__ toff = dense ? sm.off_sorted : sm.row_off;
-        if (dense) {
-            // Dense words: the node keys of the tile arrive by bulk copy, 64 words (16 KB) at a time, staged
-            // in the patch area; per node cnt = #{rows : req <= key}; the counts are kept bit-sliced
-            // (plane-major) for phase D.
-            __syncthreads();  // req_sorted is complete
-            for (uint32_t half = 0; half < 2; ++half) {
-                if (half) fetch_keys(half);
-                mbar_wait(&key_bar, key_phase);
-                key_phase ^= 1u;
-                // each warp owns words warp, warp + 8, ... of this half and runs four of them at a time, so
-                // that four independent binary searches hide each other's shared-memory latency
-                for (uint32_t i0 = warp; i0 < 64; i0 += 4 * kWarps) {
-                    uint32_t cnt[4];
-                    u64 key[4];
-                    bool on[4];
+        if (!dense && tid == 0) {  // the next tile is known: start fetching its inputs
+            sm.next_tile = gridDim.x + ticket;
+            request(sm.next_tile, stage ^ 1u);
+        }
+        GS_TRACE(3);
+
+        // D, first part: lane owns 4 words, warp owns rows warp, warp + kWarps, ...; 16 bytes per lane, 512
+        // contiguous bytes per warp and row.  Lanes whose four words are the same in every row store now.
+        const uint32_t wcol = w0 + lane * 4;
+        uint4 b4 = make_uint4(0, 0, 0, 0);
+        uint32_t p4 = 0xffffffffu;
+        if (kVec) {
+            b4 = *reinterpret_cast<const uint4*>(&sm.basew[lane * 4]);
+            p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lane * 4]);
+            if (wcol < words_out && p4 == 0xffffffffu) {
+                uint32_t* dst = out + wcol;
+#pragma unroll 4
+                for (uint32_t rr = warp; rr < rows; rr += kWarps)
+                    __stcs(reinterpret_cast<uint4*>(dst + sm.row_off[rr]), b4);
+            }
+        } else {
+            for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                uint32_t* dst = out + sm.row_off[rr] + w0;
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const uint32_t i = i0 + u * kWarps;
-                        on[u] = i < 64 && sm.pidx[half * 64 + i] == 0xfeu;  // warp-uniform
-                        key[u] = on[u] ? kstage[i * 32 + lane] : 0ull;
-                        cnt[u] = 0;
-                    }
-                    // cnt = #{rows : req <= key}: branch-free upper bound over the 64 sorted requests
-#pragma unroll
-                    for (uint32_t step = kTileRows / 2; step > 0; step >>= 1) {
-#pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            if (sm.req_sorted[cnt[u] + step - 1] <= key[u]) cnt[u] += step;
-                    }
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        if (!on[u]) continue;
-                        const uint32_t t = half * 64 + i0 + u * kWarps;
-                        uint32_t c = cnt[u];
-                        if (c == kTileRows - 1 && sm.req_sorted[kTileRows - 1] <= key[u]) c = kTileRows;
-                        c = min(c, rows);  // a key of ~0 also matches the padding rows
-                        // nodes outside `some` never pass (q' == 0 stores key 0, which would match a zero request)
-                        if (!((sm.somew[t] >> lane) & 1u)) c = 0;
-                        uint32_t mine = 0;
-#pragma unroll
-                        for (int q = 0; q < 7; ++q) {
-                            const uint32_t bal = __ballot_sync(0xffffffffu, (c >> q) & 1u);
-                            if ((int)lane == q) mine = bal;
-                        }
-                        if (lane < 7) sm.cntp[lane * kTileWords + t] = mine;  // plane-major
-                    }
+                for (int c = 0; c < kTileWords / 32; ++c) {
+                    const uint32_t wl = c * 32 + lane;
+                    if (w0 + wl < words_out && sm.pidx[wl] == 0xffu) __stcs(dst + wl, sm.basew[wl]);
                 }
-                __syncthreads();  // the staging area is reused (second half, then the patch)
             }
         }
-        if (dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);
-        // rows per sub-pass so that np patched words x rows fit the patch (odd stride spreads banks)
-        uint32_t pstride = np ? kPatchWords / np : kPatchWords;
-        pstride -= (pstride & 1u) ^ 1u;
-        const uint32_t sub_rows = min((uint32_t)kTileRows, pstride);
-        for (uint32_t r0 = 0; r0 < rows; r0 += sub_rows) {
-            const uint32_t rcount = min(sub_rows, rows - r0);
-            if (np) {
-                __syncthreads();
-                // C: words that differ from row to row
+
+        if (np) {  // uniform
+            GS_TRACE(4);
+            if (dense) {
+                // per node of every partial word: cnt = #{rows : req <= key}, kept bit-sliced (plane-major)
+                __syncthreads();  // req_sorted is complete
+                GS_TRACE(10);
+                const uint32_t passes = wide ? 2u : 1u;
+                for (uint32_t pass = 0; pass < passes; ++pass) {
+                    if (pass && tid == 0) {  // wide tile: the keys of words 64..127 replace those of 0..63
+                        fence_async_smem();
+                        mbar_expect_tx(&key_bar, kStageWords * 4u);
+                        bulk_load(stage64, fb.node_key + (size_t)(w0 + 64u) * 32, kStageWords * 4u, &key_bar);
+                    }
+                    mbar_wait(&key_bar, key_phase);
+                    key_phase ^= 1u;
+                    GS_TRACE(11);
+                    // each warp owns partial words warp, warp + 8, ... and runs four of them at a time, so
+                    // that four independent binary searches hide each other's shared-memory latency
+                    for (uint32_t k0 = warp; k0 < np; k0 += 4 * kWarps) {
+                        uint32_t cnt[4], t[4];
+                        u64 key[4];
+                        bool on[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const uint32_t k = k0 + u * kWarps;
+                            t[u] = k < np ? sm.plist[k] : 0u;
+                            on[u] = k < np && (!wide || (t[u] >> 6) == pass);  // warp-uniform
+                            key[u] = 0ull;
+                            if (on[u]) key[u] = wide ? stage64[(t[u] & 63u) * 32 + lane] : (u64)sm.stage[t[u] * 32 + lane];
+                            cnt[u] = 0;
+                        }
+                        // branch-free upper bound over the 64 sorted requests
+#pragma unroll
+                        for (uint32_t step = kTileRows / 2; step > 0; step >>= 1) {
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                if (sm.req_sorted[cnt[u] + step - 1] <= key[u]) cnt[u] += step;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (!on[u]) continue;
+                            uint32_t c = cnt[u];
+                            if (c == kTileRows - 1 && sm.req_sorted[kTileRows - 1] <= key[u]) c = kTileRows;
+                            c = min(c, rows);  // a key of ~0 also matches the padding rows
+                            // nodes outside `some` never pass (q' == 0 stores key 0, which would match a zero request)
+                            if (!((sm.somew[t[u]] >> lane) & 1u)) c = 0;
+                            uint32_t mine = 0;
+#pragma unroll
+                            for (int q = 0; q < 7; ++q) {
+                                const uint32_t bal = __ballot_sync(0xffffffffu, (c >> q) & 1u);
+                                if ((int)lane == q) mine = bal;
+                            }
+                            if (lane < 7) sm.cntp[lane * kTileWords + t[u]] = mine;
+                        }
+                    }
+                    __syncthreads();  // counts complete; the key area may be overwritten
+                }
+                if (tid == 0) {  // the ticket of a dense tile is taken late: see the schedule note above
+                    ticket = atomicAdd(&fb.sched[0], 1u);
+                    sm.next_tile = gridDim.x + ticket;
+                    request(sm.next_tile, stage ^ 1u);
+                }
+            } else {
+                // C: lane = row; the compared nodes' keys come from the staged 32 keys of the word
+                mbar_wait(&key_bar, key_phase);
+                key_phase ^= 1u;
+                uint32_t* const patch = sm.stage + kSparseKeyWords;
                 for (uint32_t k = warp; k < np; k += kWarps) {
                     const uint32_t t = sm.plist[k];
                     const uint32_t base = sm.basew[t];
-                    uint32_t* prow = &sm.patch[k * pstride];
-                    // lane = row; the compared nodes' keys come from shared memory
-                    const uint32_t eb = sm.ebits[t];
+                    uint32_t pm = sm.pmask[t];
                     u64 kk[kSparseMax];
                     uint32_t kb[kSparseMax];
 #pragma unroll
                     for (int i = 0; i < kSparseMax; ++i) {
-                        const uint32_t bit = (eb >> (8 * i)) & 0xffu;
-                        kk[i] = sm.ekey[t * kSparseMax + i];
-                        kb[i] = bit == 0xffu ? 0u : 1u << bit;
+                        kk[i] = 0;
+                        kb[i] = 0;  // unused slots set nothing
+                        if (pm) {
+                            const uint32_t bit = __ffs(pm) - 1;
+                            pm &= pm - 1;
+                            kk[i] = sm.stage[k * 32 + bit];
+                            kb[i] = 1u << bit;
+                        }
                     }
-                    for (uint32_t rr = lane; rr < rcount; rr += 32) {
-                        const u64 rq = treq[r0 + rr];
+                    for (uint32_t rr = lane; rr < rows; rr += 32) {
+                        const u64 rq = sm.req[rr];
                         uint32_t v = base;
 #pragma unroll
                         for (int i = 0; i < kSparseMax; ++i)
-                            if (kk[i] >= rq) v |= kb[i];  // unused slots have kb == 0
-                        prow[rr] = v;
+                            if (kk[i] >= rq) v |= kb[i];
+                        patch[k * kPatchStride + rr] = v;
                     }
                 }
                 __syncthreads();
             }
-            if (r0 == 0 && tid == 0) {  // the next tile is known: start fetching its inputs
-                sm.next_tile = gridDim.x + ticket;
-                request(sm.next_tile, stage ^ 1u);
-            }
-            // D: lane owns 4 words, warp owns rows r0 + warp, r0 + warp + kWarps, ...; 16 bytes per
-            // lane, 512 contiguous bytes per warp and row
+
+            // D, second part: the lanes that own a partial word
+            GS_TRACE(5);
+            const uint32_t* const patch = sm.stage + kSparseKeyWords;
+            const u64* __restrict__ toff = dense ? sm.off_sorted : sm.row_off;
             if (kVec) {
-                const uint32_t wcol = w0 + lane * 4;
-                if (wcol < words_out) {
-                    const uint4 b4 = *reinterpret_cast<const uint4*>(&sm.basew[lane * 4]);
-                    const uint32_t p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lane * 4]);
+                if (wcol < words_out && p4 != 0xffffffffu) {
                     uint32_t* dst = out + wcol;
-                    if (p4 == 0xffffffffu) {
-#pragma unroll 4
-                        for (uint32_t rr = warp; rr < rcount; rr += kWarps)
-                            __stcs(reinterpret_cast<uint4*>(dst + toff[r0 + rr]), b4);
-                    } else {
-                        const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
-                        const bool any_dense4 = k0 == 0xfeu || k1 == 0xfeu || k2 == 0xfeu || k3 == 0xfeu;
-                        for (uint32_t rr = warp; rr < rcount; rr += kWarps) {
-                            uint4 v = b4;
-                            if (k0 < 0xfeu) v.x = sm.patch[k0 * pstride + rr];
-                            if (k1 < 0xfeu) v.y = sm.patch[k1 * pstride + rr];
-                            if (k2 < 0xfeu) v.z = sm.patch[k2 * pstride + rr];
-                            if (k3 < 0xfeu) v.w = sm.patch[k3 * pstride + rr];
-                            if (any_dense4) {
-                                // dense words: bit set iff the node's pass count reaches row + 1 (warp-uniform)
-                                const uint32_t thr = r0 + rr + 1;
-                                uint4 ge = make_uint4(~0u, ~0u, ~0u, ~0u);
+                    const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
+                    if (dense) {
+                        for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                            // bit set iff the node's pass count reaches (sorted) row + 1
+                            const uint32_t thr = rr + 1;
+                            uint4 ge = make_uint4(~0u, ~0u, ~0u, ~0u);
 #pragma unroll
-                                for (int q = 0; q < 7; ++q) {
-                                    const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lane * 4]);
-                                    if ((thr >> q) & 1u) {
-                                        ge.x &= pl.x; ge.y &= pl.y; ge.z &= pl.z; ge.w &= pl.w;
-                                    } else {
-                                        ge.x |= pl.x; ge.y |= pl.y; ge.z |= pl.z; ge.w |= pl.w;
-                                    }
+                            for (int q = 0; q < 7; ++q) {
+                                const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lane * 4]);
+                                if ((thr >> q) & 1u) {
+                                    ge.x &= pl.x; ge.y &= pl.y; ge.z &= pl.z; ge.w &= pl.w;
+                                } else {
+                                    ge.x |= pl.x; ge.y |= pl.y; ge.z |= pl.z; ge.w |= pl.w;
                                 }
-                                if (k0 == 0xfeu) v.x = ge.x;
-                                if (k1 == 0xfeu) v.y = ge.y;
-                                if (k2 == 0xfeu) v.z = ge.z;
-                                if (k3 == 0xfeu) v.w = ge.w;
                             }
-                            __stcs(reinterpret_cast<uint4*>(dst + toff[r0 + rr]), v);
+                            uint4 v = b4;
+                            if (k0 != 0xffu) v.x = ge.x;
+                            if (k1 != 0xffu) v.y = ge.y;
+                            if (k2 != 0xffu) v.z = ge.z;
+                            if (k3 != 0xffu) v.w = ge.w;
+                            __stcs(reinterpret_cast<uint4*>(dst + toff[rr]), v);
+                        }
+                    } else {
+                        for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                            uint4 v = b4;
+                            if (k0 != 0xffu) v.x = patch[k0 * kPatchStride + rr];
+                            if (k1 != 0xffu) v.y = patch[k1 * kPatchStride + rr];
+                            if (k2 != 0xffu) v.z = patch[k2 * kPatchStride + rr];
+                            if (k3 != 0xffu) v.w = patch[k3 * kPatchStride + rr];
+                            __stcs(reinterpret_cast<uint4*>(dst + toff[rr]), v);
                         }
                     }
                 }
             } else {
-                for (uint32_t rr = warp; rr < rcount; rr += kWarps) {
-                    uint32_t* dst = out + toff[r0 + rr] + w0;
+                for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                    uint32_t* dst = out + toff[rr] + w0;
 #pragma unroll
                     for (int c = 0; c < kTileWords / 32; ++c) {
                         const uint32_t wl = c * 32 + lane;
-                        if (w0 + wl < words_out) {
-                            const uint32_t k = sm.pidx[wl];
-                            uint32_t v = sm.basew[wl];
-                            if (k < 0xfeu) {
-                                v = sm.patch[k * pstride + rr];
-                            } else if (k == 0xfeu) {
-                                const uint32_t thr = r0 + rr + 1;
+                        const uint32_t k = sm.pidx[wl];
+                        if (w0 + wl < words_out && k != 0xffu) {
+                            uint32_t v;
+                            if (dense) {
+                                const uint32_t thr = rr + 1;
                                 v = ~0u;
 #pragma unroll
                                 for (int q = 0; q < 7; ++q) {
                                     const uint32_t pl = sm.cntp[q * kTileWords + wl];
                                     v = ((thr >> q) & 1u) ? (v & pl) : (v | pl);
                                 }
+                            } else {
+                                v = patch[k * kPatchStride + rr];
                             }
                             __stcs(dst + wl, v);
                         }
@@ -715,11 +784,13 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                 }
             }
         }
-        if (tid == 0) {  // everyone copied these to registers before the barriers above (or they are 0)
+        if (tid == 0) {  // everyone copied these to registers right after phase A
+            GS_TRACE(6);
             sm.n_partial = 0;
-            sm.n_dense = 0;
+            sm.n_heavy = 0;
         }
-        __syncthreads();  // phase A of the next tile rewrites what phase D was reading
+        __syncthreads();  // phase A of the next tile rewrites what this tile was reading
+        GS_TRACE(7);
         cur = sm.next_tile;
     }
     // the last CTA out re-arms the ticket counter for the next launch
@@ -822,3 +893,10 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
 }
 
 }  // namespace gs
+
+#ifdef GS_EXPAND_TRACE
+extern "C" int gs_debug_expand_trace(unsigned long long* host, size_t n) {
+    if (n > sizeof(gs::g_trace) / 8) n = sizeof(gs::g_trace) / 8;
+    return (int)cudaMemcpyFromSymbol(host, gs::g_trace, n * 8);
+}
+#endif

@@ -18,6 +18,7 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     uint32_t* pod_hist;               // [512 + 2] bucket counts, arrived / finished block counters (self re-arming)
     uint32_t* planes;                 // [words / kTileWords][kRankPlanes][kTileWords] node bucket ids, bit-sliced
     unsigned long long* node_key;     // [words * 32] max available memory per node
+    uint32_t* node_key32;             // [words * 32] the same, saturated to 32 bits
     uint32_t* sched;                  // [2] tile scheduler of k_expand (self re-arming)
 };
 cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n, unsigned long long* d_sorted,

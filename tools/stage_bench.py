@@ -38,6 +38,13 @@ def main():
         "mid(50k-100k)": rng.integers(50000, 100000, P),
         "top(180k-184k)": rng.integers(180000, 184320, P),
         "too_big(>200k)": rng.integers(200000, 400000, P),
+        "zero_req": np.zeros(P, dtype=np.int64),
+        "big_spread(200k-260k)": rng.integers(200000, 260000, P),
+        "huge(1e6)": np.full(P, 1000000, dtype=np.int64),
+        "one(150000)": np.full(P, 150000, dtype=np.int64),
+        "one(261000)": np.full(P, 261000, dtype=np.int64),
+        "one(261631)": np.full(P, 261631, dtype=np.int64),
+        "one(261632)": np.full(P, 261632, dtype=np.int64),
     }
     only = os.environ.get("CASE")
     for name, reqs in cases.items():
