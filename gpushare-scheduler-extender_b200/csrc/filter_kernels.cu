@@ -866,7 +866,13 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
         if (ea != cudaSuccess) return ea;
     }
     const bool vec = (row_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_out) & 15u) == 0);
-    const uint32_t words_out = vec ? ((words + 3u) & ~3u) : words;
+    // 16-byte stores; the row's last 32-byte sector is written whole when the stride leaves room for it (a
+    // half-written sector costs a read-modify-write in DRAM: profiles/NOTES.md).  Padding bits are zero.
+    uint32_t words_out = words;
+    if (vec) {
+        words_out = (words + 7u) & ~7u;
+        if (words_out > row_stride) words_out = (words + 3u) & ~3u;
+    }
     const uint32_t n_col_blocks = (words_out + kTileWords - 1) / kTileWords;
     const uint32_t n_row_tiles = (n_pods + kTileRows - 1) / kTileRows;
     const uint32_t n_tiles = n_col_blocks * n_row_tiles;

@@ -159,9 +159,10 @@ int gs_pods_apply(gs_snapshot* s, const gs_pod_event* events, uint32_t n);
 /* K3: the Predicate.Handler loop for a batch of pending pods against every node.
  * req[p] = uint(GetGPUMemoryFromPodResource(pod p)).  out_bitmap is [n_pods][row_stride_words]
  * 32-bit words, bit (n & 31) of word (n >> 5) of row p set iff the predicate passes for node n;
- * row_stride_words >= ceil(node_count / 32); padding words up to the next multiple of 4 may be
- * written as zero.  A zero bit on a GS_NODE_OK node means "Insufficient GPU Memory in one device".
- * Fastest when row_stride_words is a multiple of 4 and out_bitmap came from gs_host_alloc. */
+ * row_stride_words >= ceil(node_count / 32); padding words up to the next multiple of 8 (whole
+ * 32-byte sectors), as far as they lie inside the row stride, may be written as zero.  A zero bit on a
+ * GS_NODE_OK node means "Insufficient GPU Memory in one device".  Fastest when row_stride_words is a
+ * multiple of 8 and out_bitmap came from gs_host_alloc. */
 int gs_filter_batch(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint32_t* out_bitmap,
                     uint32_t row_stride_words);
 /* Same, with req and out_bitmap in device memory of the snapshot's GPU; asynchronous on

@@ -57,7 +57,8 @@ __global__ void k_tile2(uint4* out, int n_rows, int pitch16, int cb_count, int s
 // feeding the stored value, 8 = row offsets read from shared memory, 16 = 100 dependent ALU ops per tile
 template <int MODE>
 __global__ void k_tile3(uint4* out, int n_rows, int pitch16, int cb_count, int seg16, int tile_rows,
-                        unsigned* sched, const unsigned* __restrict__ aux) {
+                        unsigned* sched, const unsigned* __restrict__ aux, int cols16 = 0) {
+    if (cols16 == 0) cols16 = pitch16;
     __shared__ unsigned s_tile;
     __shared__ unsigned long long s_off[64];
     int n_tiles = (n_rows / tile_rows) * cb_count;
@@ -70,7 +71,8 @@ __global__ void k_tile3(uint4* out, int n_rows, int pitch16, int cb_count, int s
             t = s_tile;
         }
         if (t >= n_tiles) break;
-        int rt = t / cb_count, cb = t % cb_count;
+        int tt = (MODE & 32) ? n_tiles - 1 - t : t;
+        int rt = tt / cb_count, cb = tt % cb_count;
         unsigned x = 1;
         if (MODE & 4) x = aux[(t * 131 + threadIdx.x) & 0xffff];
         if (MODE & 16) {
@@ -85,7 +87,7 @@ __global__ void k_tile3(uint4* out, int n_rows, int pitch16, int cb_count, int s
             for (int c = lane; c < seg16; c += 32) {
                 int col = cb * seg16 + c;
                 size_t off = (MODE & 8) ? s_off[r] : (size_t)(rt * tile_rows + r) * pitch16;
-                if (col < pitch16) __stcs(&out[off + col], make_uint4(x, 2, 3, 4));
+                if (col < cols16) __stcs(&out[off + col], make_uint4(x, 2, 3, 4));
             }
         if (MODE & 1) __syncthreads();
         if (!(MODE & 2)) { t += gridDim.x; }
@@ -131,6 +133,17 @@ int main() {
     unsigned* sched; cudaMalloc(&sched, 8); cudaMemset(sched, 0, 8);
     unsigned* aux; cudaMalloc(&aux, 65536 * 4); cudaMemset(aux, 1, 65536 * 4);
 #define RUN3(M) run("k_tile3 mode " #M, [&](uint4* o) { k_tile3<M><<<740, 256>>>(o, rows, 392, 13, 32, 64, sched, aux); });
-    RUN3(1) RUN3(9) RUN3(17) RUN3(25) RUN3(29) RUN3(31)
+    RUN3(0) RUN3(1) RUN3(9) RUN3(11)
+    // the real layout: 10000 rows (156 full row tiles here), pitch 6400 B, 1564 words used
+    for (auto& b : buf) { cudaFree(b); cudaMalloc(&b, (size_t)10048 * 6400); }
+#define RUN4(M) run("pitch 6400: k_tile3 mode " #M, [&](uint4* o) { k_tile3<M><<<740, 256>>>(o, rows, 400, 13, 32, 64, sched, aux, 391); });
+    RUN4(0) RUN4(32) RUN4(9) RUN4(2) RUN4(11) RUN4(43)
+    // row pitch sweep, 391 x 16 B used per row, static round-robin tiles of 64 rows x 512 B
+    for (auto& b : buf) { cudaFree(b); cudaMalloc(&b, (size_t)10048 * 8192); }
+    for (int p16 : {391, 392, 394, 396, 400, 404, 408, 416, 424, 448, 512}) {
+        char name[96];
+        snprintf(name, sizeof name, "pitch %d B static", p16 * 16);
+        run(name, [&](uint4* o) { k_tile3<0><<<740, 256>>>(o, rows, p16, 13, 32, 64, sched, aux, 391); });
+    }
     return 0;
 }
