@@ -149,7 +149,10 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     const uint32_t words_pad = (words + gs::kTileWords - 1) / gs::kTileWords * gs::kTileWords;
     if (words_pad > s->rank_words) return fail(GS_ERR_CAPACITY, "rank planes too small");
     const uint32_t set = s->fb_set;
-    if (stages == 7u) s->fb_set ^= 1u;  // full launches alternate; single-stage profiling launches stay on one set
+    // full launches alternate; single-stage profiling launches stay on one set (development builds can let
+    // expand-only launches alternate and overlap too: GS_EXPAND_TRACE + option value 2)
+    const bool dev_overlap_expand = s->pipeline_dev && stages == GS_STAGE_EXPAND;
+    if (stages == 7u || dev_overlap_expand) s->fb_set ^= 1u;
     gs::FilterBuffers fb;
     fb.grouped_req = s->d_sorted_keys + (size_t)set * GS_MAX_BATCH;
     fb.perm = s->d_perm + (size_t)set * GS_MAX_BATCH;
@@ -159,13 +162,18 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     fb.node_key = s->d_node_key + (size_t)set * s->rank_words * 32;
     fb.node_key32 = s->d_node_key32 + (size_t)set * s->rank_words * 32;
     fb.sched = s->d_sched + set * 2;
+    fb.set_index = set;
+    fb.prep_done = s->d_epochs + 3 * set;
+    fb.prep_epoch = s->d_epochs + 3 * set + 1;
+    fb.expand_epoch = s->d_epochs + 3 * set + 2;
     // With GS_OPT_PIPELINE_FILTERS, a filter that directly follows another filter of this snapshot on the same
     // stream, writing somewhere else, does not wait for that filter's expand kernel to drain before its own prep
     // kernel starts (the two touch different work-buffer sets).  Anything else keeps plain stream order.
     const char* out_lo = reinterpret_cast<const char*>(d_out);
     const char* out_hi = out_lo + (size_t)n_pods * row_stride * sizeof(uint32_t);
-    const bool overlap_ok = s->pipeline && stages == 7u && s->prev_filter && s->prev_stream == st &&
-                            (out_hi <= s->prev_out_lo || out_lo >= s->prev_out_hi);
+    const bool overlap_ok = dev_overlap_expand ||
+                            (s->pipeline && stages == 7u && s->prev_filter && s->prev_stream == st &&
+                             (out_hi <= s->prev_out_lo || out_lo >= s->prev_out_hi));
     // bucket scale: requests up to the largest device capacity spread over all 512 buckets
     uint32_t bits = 0;
     while (bits < 64 && (s->max_capacity >> bits) != 0) ++bits;
@@ -174,13 +182,20 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     const bool do_pods = (stages & GS_STAGE_SORT) != 0, do_nodes = (stages & GS_STAGE_NODE_RANK) != 0;
     if (do_pods || do_nodes)
         rc = timed(s, do_pods ? GS_K_SORT : GS_K_NODE_RANK, st, 1, [&] {
-            return gs::launch_prep(d_req, n_pods, do_pods, do_nodes, shift, fb, s->d_used, s->d_cap, s->d_nodeinfo,
-                                   s->n_nodes, s->max_devs, words_pad, overlap_ok, st);
+            cudaError_t e = gs::launch_prep(d_req, n_pods, do_pods, do_nodes, shift, fb, s->d_used, s->d_cap, s->d_nodeinfo,
+                                            s->n_nodes, s->max_devs, words_pad, overlap_ok, s->n_expand[set], st);
+            if (e == cudaSuccess) ++s->n_prep[set];
+            return e;
         });
     if (rc) return rc;
     if (stages & GS_STAGE_EXPAND)
         rc = timed(s, GS_K_EXPAND, st, 1,
-                   [&] { return gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, st); });
+                   [&] {
+                       cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok,
+                                                         s->n_prep[set], st);
+                       if (e == cudaSuccess) ++s->n_expand[set];
+                       return e;
+                   });
     s->prev_filter = rc == GS_OK && stages == 7u && !s->profiling;
     s->prev_stream = st;
     s->prev_out_lo = out_lo;
@@ -264,6 +279,8 @@ int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32
     CU_NEW(cudaMalloc(&s->d_row_bucket, 2 * (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
     CU_NEW(cudaMalloc(&s->d_pod_hist, 516 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 516 * sizeof(uint32_t), s->stream));
+    CU_NEW(cudaMalloc(&s->d_epochs, 6 * sizeof(uint32_t)));
+    CU_NEW(cudaMemsetAsync(s->d_epochs, 0, 6 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMalloc(&s->d_sched, 4 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_sched, 0, 4 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_used, 0, (size_t)max_nodes * max_devs * sizeof(u64), s->stream));
@@ -296,6 +313,7 @@ int gs_snapshot_destroy(gs_snapshot* s) {
     cudaFree(s->d_row_bucket);
     cudaFree(s->d_pod_hist);
     cudaFree(s->d_sched);
+    cudaFree(s->d_epochs);
     cudaFree(s->d_stage);
     cudaFree(s->d_bitmap);
     if (s->h_stage) cudaFreeHost(s->h_stage);
@@ -590,6 +608,9 @@ int gs_set_option(gs_snapshot* s, int option, int value) {
     Guard g(s);
     if (option == GS_OPT_PIPELINE_FILTERS) {
         s->pipeline = value != 0;
+#ifdef GS_EXPAND_TRACE
+        s->pipeline_dev = value == 2;
+#endif
         s->prev_filter = false;
         return GS_OK;
     }

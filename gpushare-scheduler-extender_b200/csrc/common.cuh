@@ -60,7 +60,11 @@ struct gs_snapshot {
     // launches alternate between them, so that with GS_OPT_PIPELINE_FILTERS the prep kernel of one batch can run
     // under the tail of the previous batch's expand kernel.
     uint32_t fb_set = 0;
+    uint32_t* d_epochs = nullptr;     // per set s: [3 * s] finished k_prep blocks, [3 * s + 1] k_prep epoch, [3 * s + 2] k_expand epoch
+    uint32_t n_prep[2] = {0, 0};      // k_prep / k_expand launches issued per set (what the epochs will reach)
+    uint32_t n_expand[2] = {0, 0};
     bool pipeline = false;            // GS_OPT_PIPELINE_FILTERS
+    bool pipeline_dev = false;        // development builds: expand-only launches overlap as well
     bool prev_filter = false;         // the last operation enqueued for this snapshot was a filter ...
     cudaStream_t prev_stream = nullptr;  // ... on this stream ...
     const char* prev_out_lo = nullptr;   // ... writing [prev_out_lo, prev_out_hi)

@@ -215,6 +215,34 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
 // so that for a closed bucket b'  q' > b' implies key >= every request in it and q' < b' implies
 // key < all of them.  q' is written bit-sliced, plane-major inside blocks of kTileWords words:
 //   planes[((word / kTileWords) * kRankPlanes + k) * kTileWords + word % kTileWords] = bit k of 32 q'.
+#ifdef GS_EXPAND_TRACE
+// development builds only: per launch (ring of 64), per kernel (0 = k_prep, 1 = k_expand), earliest / latest
+// globaltimer of: 0 block entry, 1 past the start wait, 2 block exit (tools/overlap_trace.py)
+__device__ unsigned long long g_kmin[64][2][6];
+__device__ unsigned long long g_kmax[64][2][6];
+__device__ __forceinline__ void ktrace(uint32_t seq, int kernel, int what) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
+    atomicMin(&g_kmin[seq & 63][kernel][what], gt);
+    atomicMax(&g_kmax[seq & 63][kernel][what], gt);
+}
+#define GS_KTRACE(seq, kernel, what) do { if (threadIdx.x == 0) ktrace(seq, kernel, what); } while (0)
+#else
+#define GS_KTRACE(seq, kernel, what) do {} while (0)
+#endif
+
+// Epoch counters let consecutive filter batches overlap without stream-order waits: a kernel publishes "done"
+// by bumping a counter after a fence, a later kernel that really depends on it spins on the counter.
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void wait_epoch(const uint32_t* p, uint32_t want) {
+    while ((int32_t)(ld_acquire_u32(p) - want) < 0) {
+    }
+}
+
 constexpr int kPrepThreads = 128;  // small blocks: they fit next to a fully resident k_expand of the previous batch
 constexpr uint32_t kBuckets = 512;
 
@@ -227,88 +255,19 @@ __device__ __forceinline__ u64 node_key_generic(const u64* __restrict__ used_row
     return key;
 }
 
-template <int kDevStride>
-__global__ void __launch_bounds__(kPrepThreads)
-k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32_t shift, FilterBuffers fb,
-       const u64* __restrict__ used, const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
-       uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, uint32_t overlap_previous) {
+// Both roles read their inputs first and hold their results in registers; `may_write()` is called (by every
+// thread of the block) before the first store into the buffer set.
+template <int kDevStride, class MayWrite>
+__device__ __forceinline__ void prep_node_role(uint32_t block, const FilterBuffers& fb, const u64* __restrict__ used,
+                                               const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
+                                               uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, uint32_t shift,
+                                               MayWrite may_write) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // Programmatic dependent launch, both ways.  This grid is launched as a programmatic dependent of whatever
-    // precedes it in the stream: normally it waits for that work to complete and flush; only when the host knows
-    // the predecessor is the expand kernel of another filter batch that shares nothing with this one does it run
-    // under that kernel's tail.  And k_expand may start its prologue now; it waits (griddepcontrol.wait) for
-    // this grid to complete before it reads anything written here.
-    if (!overlap_previous) asm volatile("griddepcontrol.wait;" ::: "memory");
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    if (blockIdx.x < pod_blocks) {
-        // ---------------- pod role ----------------
-        __shared__ uint32_t base[kBuckets];
-        __shared__ uint32_t wsum[kPrepThreads / 32];
-        __shared__ bool is_last;
-        constexpr int kPer = kBuckets / kPrepThreads;  // buckets scanned per thread
-        static_assert(kPer == 4, "the scan below reads four counts per thread");
-        uint32_t* ghist = fb.pod_hist;  // [kBuckets] counts, [kBuckets] arrived blocks, [kBuckets + 1] finished blocks
-        const uint32_t i = blockIdx.x * kPrepThreads + tid;
-        uint32_t sl = 0;
-        u64 r = 0;
-        if (i < n_pods) {
-            r = req[i];
-            const u64 bq = r >> shift;
-            const uint32_t b = bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1;
-            sl = (b << 16) | atomicAdd(&ghist[b], 1u);  // arrival number inside the bucket
-        }
-        // barrier among the pod blocks (the first blocks of a small grid of small blocks: all of them become
-        // resident, even next to another kernel): the bucket counts are complete once every block has arrived
-        __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            atomicAdd(&ghist[kBuckets], 1u);
-            while (atomicAdd(&ghist[kBuckets], 0u) < pod_blocks) {
-            }
-            __threadfence();
-        }
-        __syncthreads();
-        // bucket counts -> offsets (every block scans the 512 counts itself), then the block's own pods
-        const uint4 c4 = __ldcg(reinterpret_cast<const uint4*>(ghist) + tid);
-        const uint32_t sum = c4.x + c4.y + c4.z + c4.w;
-        uint32_t incl = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-            if ((int)lane >= o) incl += t;
-        }
-        if (lane == 31) wsum[warp] = incl;
-        __syncthreads();
-        uint32_t run = incl - sum;
-        for (uint32_t w = 0; w < warp; ++w) run += wsum[w];
-        base[tid * 4 + 0] = run;
-        base[tid * 4 + 1] = run + c4.x;
-        base[tid * 4 + 2] = run + c4.x + c4.y;
-        base[tid * 4 + 3] = run + c4.x + c4.y + c4.z;
-        __syncthreads();
-        if (i < n_pods) {
-            const uint32_t b = sl >> 16;
-            const uint32_t j = base[b] + (sl & 0xffffu);
-            fb.perm[j] = (uint16_t)i;
-            fb.grouped_req[j] = r;
-            fb.row_bucket[j] = (uint16_t)(b + 1);  // bucket ids are stored 1-based
-        }
-        // every block has read the counts once it is here; the last one out re-arms them
-        if (tid == 0) is_last = atomicAdd(&ghist[kBuckets + 1], 1u) == pod_blocks - 1;
-        __syncthreads();
-        if (is_last) {
-            reinterpret_cast<uint4*>(ghist)[tid] = make_uint4(0, 0, 0, 0);
-            if (tid < 2) ghist[kBuckets + tid] = 0;
-        }
-        return;
-    }
-    // ---------------- node role ----------------
-    const uint32_t word = (blockIdx.x - pod_blocks) * (kPrepThreads / 32) + warp;
-    if (word >= n_words) return;
+    const uint32_t word = block * (kPrepThreads / 32) + warp;
     const uint32_t node = word * 32 + lane;
     uint32_t q = 0;
     u64 key = 0;
-    if (node < n_nodes) {
+    if (word < n_words && node < n_nodes) {
         const uint32_t info = nodeinfo[node];
         const uint32_t ndev = nodeinfo_ndev(info);
         if (nodeinfo_class(info) == GS_NODE_OK && ndev > 0) {
@@ -329,16 +288,134 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
             q = 1u + (uint32_t)(bq < kBuckets ? bq : kBuckets);
         }
     }
-    fb.node_key[node] = key;
-    fb.node_key32[node] = key > 0xffffffffull ? 0xffffffffu : (uint32_t)key;  // exact against any request below 2^32
     uint32_t mine = 0;
 #pragma unroll
     for (int k = 0; k < kRankPlanes; ++k) {
         uint32_t b = __ballot_sync(0xffffffffu, (q >> k) & 1u);
         if ((int)lane == k) mine = b;
     }
+    may_write();
+    if (word >= n_words) return;
+    fb.node_key[node] = key;
+    fb.node_key32[node] = key > 0xffffffffull ? 0xffffffffu : (uint32_t)key;  // exact against any request below 2^32
     if (lane < kRankPlanes)
         fb.planes[((size_t)(word / kTileWords) * kRankPlanes + lane) * kTileWords + (word % kTileWords)] = mine;
+}
+
+template <int kDevStride>
+__global__ void __launch_bounds__(kPrepThreads)
+k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32_t shift, FilterBuffers fb,
+       const u64* __restrict__ used, const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
+       uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, uint32_t overlap_previous,
+       uint32_t expand_epoch_wanted) {
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ bool is_last;
+    // Programmatic dependent launch, both ways.  This grid is launched as a programmatic dependent of whatever
+    // precedes it in the stream: normally it waits for that work to complete and flush.  Only when the host knows
+    // that the predecessor is the expand kernel of another filter batch, which shares nothing with this one, does
+    // it start at once; what it must not do then is overwrite work buffers that an older expand kernel (the one
+    // that last used this buffer set) may still be reading.  That kernel's epoch is read now and checked just
+    // before the first store into the set, so the round trip overlaps the loads below (a round trip to L2
+    // costs microseconds on an SM that is streaming the previous batch's bitmap).
+    // k_expand may start its prologue as soon as every block here has started; it waits for this grid's own
+    // epoch before it reads anything written here.
+    GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 0);
+    uint32_t epoch_seen = expand_epoch_wanted;
+    if (!overlap_previous) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    } else if (tid == 0) {
+        epoch_seen = ld_acquire_u32(fb.expand_epoch);
+    }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    auto may_write = [&]() {
+        if (tid == 0 && (int32_t)(epoch_seen - expand_epoch_wanted) < 0) wait_epoch(fb.expand_epoch, expand_epoch_wanted);
+        __syncthreads();
+        GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 1);
+    };
+    if (blockIdx.x < pod_blocks) {
+        // ---------------- pod role ----------------
+        __shared__ uint32_t base[kBuckets];
+        __shared__ uint32_t wsum[kPrepThreads / 32];
+        constexpr int kPer = kBuckets / kPrepThreads;  // buckets scanned per thread
+        static_assert(kPer == 4, "the scan below reads four counts per thread");
+        uint32_t* ghist = fb.pod_hist;  // [kBuckets] bucket counts, zero between launches
+        const uint32_t i = blockIdx.x * kPrepThreads + tid;
+        uint32_t sl = 0;
+        u64 r = 0;
+        if (i < n_pods) {
+            r = req[i];
+            const u64 bq = r >> shift;
+            const uint32_t b = bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1;
+            sl = (b << 16) | atomicAdd(&ghist[b], 1u);  // arrival number inside the bucket
+        }
+        if (sl == 0xffffffffu) return;  // (never true: makes the stamp below wait for the atomic's result)
+        GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 3);
+        // The counts are complete when they add up to the number of pods: every block polls the 512 counts (the
+        // pod blocks are the first blocks of a small grid of small blocks: all of them are resident), and the
+        // poll that finds them complete already holds the values the scan needs.
+        uint4 c4;
+        uint32_t run;
+        for (;;) {
+            c4 = __ldcg(reinterpret_cast<const uint4*>(ghist) + tid);
+            const uint32_t sum = c4.x + c4.y + c4.z + c4.w;
+            uint32_t incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                if ((int)lane >= o) incl += t;
+            }
+            if (lane == 31) wsum[warp] = incl;
+            __syncthreads();
+            run = incl - sum;
+            uint32_t total = 0;
+#pragma unroll
+            for (uint32_t w = 0; w < kPrepThreads / 32; ++w) {
+                const uint32_t ws = wsum[w];
+                total += ws;
+                if (w < warp) run += ws;
+            }
+            __syncthreads();  // wsum is rewritten by the next poll
+            if (total == n_pods) break;
+        }
+        GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 4);
+        base[tid * 4 + 0] = run;
+        base[tid * 4 + 1] = run + c4.x;
+        base[tid * 4 + 2] = run + c4.x + c4.y;
+        base[tid * 4 + 3] = run + c4.x + c4.y + c4.z;
+        may_write();  // also orders the writes of `base` before the reads below
+        if (i < n_pods) {
+            const uint32_t b = sl >> 16;
+            const uint32_t j = base[b] + (sl & 0xffffu);
+            fb.perm[j] = (uint16_t)i;
+            fb.grouped_req[j] = r;
+            fb.row_bucket[j] = (uint16_t)(b + 1);  // bucket ids are stored 1-based
+        }
+    } else {
+        prep_node_role<kDevStride>(blockIdx.x - pod_blocks, fb, used, cap, nodeinfo, n_nodes, dev_stride, n_words, shift,
+                                   may_write);
+    }
+    // Done: the last block out clears the bucket counts for the next launch (every pod block has read them by
+    // then) and publishes this launch; everything written above is fenced first.
+    __syncthreads();
+    GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 2);
+    if (tid == 0) {
+        __threadfence();
+        is_last = atomicAdd(fb.prep_done, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last) {
+        reinterpret_cast<uint4*>(fb.pod_hist)[tid] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+        if (tid == 0) {
+            *fb.prep_done = 0;
+            __threadfence();
+            atomicAdd(fb.prep_epoch, 1u);
+            // A grid that did not wait at its start must still not complete before its predecessor does: later
+            // work in the stream relies on completion being transitive.  One lingering thread is enough to hold
+            // the grid open; every other block frees its SM resources at once.
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -452,7 +529,8 @@ __device__ unsigned long long g_trace[148 * 5 * kTraceTiles * kTraceSlots];
 template <bool kVec>
 __global__ void __launch_bounds__(kExpandThreads, 5)
 k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_stride, uint32_t* __restrict__ out,
-         uint32_t n_col_blocks, uint32_t inv_col_blocks, uint32_t n_tiles) {
+         uint32_t n_col_blocks, uint32_t inv_col_blocks, uint32_t n_tiles, uint32_t overlap_previous,
+         uint32_t prep_epoch_wanted) {
     __shared__ __align__(128) ExpandSmem sm;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr uint32_t kWarps = kExpandThreads / 32;
@@ -478,11 +556,13 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         bulk_load(in.bucket, fb.row_bucket + j0, sizeof(in.bucket), &tin_bar[stage]);
     };
 
-    // Tile schedule: the first tile of a CTA is blockIdx.x; every later one is a ticket taken during the
-    // current tile (after its dense work, if any), so a CTA never holds more than one tile ahead and
-    // CTAs stuck in a dense tile simply take fewer.  (Tickets taken several tiles ahead hoard when there
-    // are only ~3 tiles per CTA: profiles/NOTES.md.)
-    uint32_t ticket = 0;  // thread 0
+    // Tile schedule: the first tile of a CTA is blockIdx.x, every later one a ticket.  Under a saturating
+    // store stream a round trip to L2 takes ~2 us, and a tile needs two of them in sequence (the ticket, then
+    // the inputs the ticket names), which is more than the ~2.7 us a tile may take.  So the chain runs two tiles
+    // ahead: at the top of tile i the ticket asked for during tile i - 1 names tile i + 1, whose inputs are
+    // requested at once, and the ticket for tile i + 2 is asked for.  (Holding tiles ahead makes the end of a
+    // lone launch ragged; back-to-back launches overlap and fill each other's ends.)
+    uint32_t ticket = 0;  // thread 0: the ticket in flight
     if (tid == 0) {
 #pragma unroll
         for (int i = 0; i < kPrefetch; ++i) mbar_init(&tin_bar[i], 1);
@@ -491,11 +571,27 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         sm.n_partial = 0;
         sm.n_heavy = 0;
     }
-    // everything above overlapped the tail of k_prep; its results are needed from here on.  After the wait,
-    // everything that precedes this grid in the stream is complete, so a following grid may be let in.
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // Everything above overlapped the tail of k_prep; its results are needed from here on.  Normally this
+    // grid waits for all earlier work in the stream.  When the host knows that the work before this batch's
+    // k_prep is the expand kernel of another batch (other work buffers, other output), this grid only waits for
+    // its own k_prep, by epoch, and so fills the SM slots that the previous expand kernel frees one by one
+    // instead of idling through its tail.  A following grid is let in after that point.
+    GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 0);
+    if (!overlap_previous) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    } else {
+        if (tid == 0) {
+            wait_epoch(fb.prep_epoch, prep_epoch_wanted);
+            asm volatile("fence.proxy.async;" ::: "memory");  // the bulk copies below read what k_prep wrote
+        }
+        __syncthreads();
+    }
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    if (tid == 0) request(blockIdx.x, 0);
+    GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 1);
+    if (tid == 0) {
+        request(blockIdx.x, 0);
+        ticket = atomicAdd(&fb.sched[0], 1u);
+    }
     __syncthreads();
     uint32_t cur = blockIdx.x;
 
@@ -508,9 +604,35 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         const uint32_t w0 = cb * kTileWords;
         const TileInputs& in = tin[stage];
         GS_TRACE(0);
+        if (tid == 0) {
+            sm.next_tile = gridDim.x + ticket;
+            request(sm.next_tile, (it + 1) % kPrefetch);
+            ticket = atomicAdd(&fb.sched[0], 1u);
+        }
         mbar_wait(&tin_bar[stage], parity);
         GS_TRACE(1);
 
+#ifdef GS_EXPERIMENT
+        {   // timing experiments only (wrong results): 1 = stores straight from the inputs (no phase A),
+            // 2 = constant words and identity rows (inputs still fetched), 3 = as 2 with 16 warps' worth of rows per warp halved
+            constexpr int kExp = GS_EXPERIMENT;
+            if (kVec) {
+                const uint32_t wcol_ = w0 + lane * 4;
+                const uint4 b4_ = kExp == 1 ? *reinterpret_cast<const uint4*>(&in.planes[lane * 4]) : make_uint4(tile, 1, 2, 3);
+                if (wcol_ < words_out) {
+                    uint32_t* dst = out + wcol_;
+#pragma unroll 4
+                    for (uint32_t rr = warp; rr < rows; rr += kWarps)
+                        __stcs(reinterpret_cast<uint4*>(dst + (u64)(kExp == 1 ? (uint32_t)in.perm[rr] : j0 + rr) * row_stride), b4_);
+                }
+            }
+            __syncthreads();
+            const uint32_t next_ = sm.next_tile;
+            __syncthreads();
+            cur = next_;
+            continue;
+        }
+#endif
         // A: one thread per word (threads 0..127), one per row (threads 128..191)
         uint32_t my_pi = 0xffu;  // threads 0..127: position of the thread's word among the partial ones
         int big_req = 0;         // threads 128..191: the row's request does not fit 32 bits
@@ -576,8 +698,6 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             }
         }
 
-        if (!dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);  // consumed just before the stores
-
         // Dense tiles want the tile's rows in ascending request order: then a node's column is a prefix of
         // ones and one binary search per node replaces a comparison per row.
         if (dense && tid < kTileRows) {
@@ -590,10 +710,6 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             }
             sm.req_sorted[rank] = mine;
             sm.off_sorted[rank] = sm.row_off[tid];
-        }
-        if (!dense && tid == 0) {  // the next tile is known: start fetching its inputs
-            sm.next_tile = gridDim.x + ticket;
-            request(sm.next_tile, stage ^ 1u);
         }
         GS_TRACE(3);
 
@@ -678,11 +794,6 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                         }
                     }
                     __syncthreads();  // counts complete; the key area may be overwritten
-                }
-                if (tid == 0) {  // the ticket of a dense tile is taken late: see the schedule note above
-                    ticket = atomicAdd(&fb.sched[0], 1u);
-                    sm.next_tile = gridDim.x + ticket;
-                    request(sm.next_tile, stage ^ 1u);
                 }
             } else {
                 // C: lane = row; the compared nodes' keys come from the staged 32 keys of the word
@@ -789,16 +900,23 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             sm.n_partial = 0;
             sm.n_heavy = 0;
         }
+        const uint32_t next = sm.next_tile;  // written at the top of this tile; rewritten at the top of the next
         __syncthreads();  // phase A of the next tile rewrites what this tile was reading
         GS_TRACE(7);
-        cur = sm.next_tile;
+        cur = next;
     }
-    // the last CTA out re-arms the ticket counter for the next launch
+    GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 2);
+    // the last CTA out re-arms the ticket counter for the next launch and publishes this one
     if (tid == 0) {
         __threadfence();
         if (atomicAdd(&fb.sched[1], 1u) == gridDim.x - 1) {
             fb.sched[0] = 0;
             fb.sched[1] = 0;
+            __threadfence();
+            atomicAdd(fb.expand_epoch, 1u);
+            // completion stays transitive along the stream even when this grid did not wait at its start
+            // (one lingering thread holds the grid open)
+            asm volatile("griddepcontrol.wait;" ::: "memory");
         }
     }
 }
@@ -834,10 +952,10 @@ cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n
 cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do_nodes, uint32_t shift,
                         const FilterBuffers& fb, const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo,
                         uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, bool overlap_previous,
-                        cudaStream_t st) {
+                        uint32_t expand_epoch_wanted, cudaStream_t st) {
     const uint32_t pod_blocks = do_pods ? (n_pods + kPrepThreads - 1) / kPrepThreads : 0u;
     const uint32_t node_blocks = do_nodes ? (n_words + kPrepThreads / 32 - 1) / (kPrepThreads / 32) : 0u;
-    if (pod_blocks + node_blocks == 0) return cudaSuccess;
+    if (pod_blocks + node_blocks == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(pod_blocks + node_blocks);
     cfg.blockDim = dim3(kPrepThreads);
@@ -851,14 +969,15 @@ cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do
     const uint32_t ov = overlap_previous ? 1u : 0u;
     if (dev_stride == 8)
         return cudaLaunchKernelEx(&cfg, k_prep<8>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
-                                  dev_stride, n_words, ov);
+                                  dev_stride, n_words, ov, expand_epoch_wanted);
     return cudaLaunchKernelEx(&cfg, k_prep<0>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
-                              dev_stride, n_words, ov);
+                              dev_stride, n_words, ov, expand_epoch_wanted);
 }
 
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
-                          uint32_t row_stride, uint32_t* d_out, cudaStream_t st) {
-    if (n_pods == 0 || words == 0) return cudaSuccess;
+                          uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted,
+                          cudaStream_t st) {
+    if (n_pods == 0 || words == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
     {
         int dev = 0;
         cudaGetDevice(&dev);
@@ -876,7 +995,12 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
     const uint32_t n_col_blocks = (words_out + kTileWords - 1) / kTileWords;
     const uint32_t n_row_tiles = (n_pods + kTileRows - 1) / kTileRows;
     const uint32_t n_tiles = n_col_blocks * n_row_tiles;
-    const uint32_t per_sm = 5;  // resident CTAs per SM (256 threads, 48 registers, 42 KB shared)
+    // Four CTAs per SM stream as fast as five (tools/chunk_write_bw.cu), and the fifth slot's registers and
+    // threads are what lets every block of the next batch's k_prep become resident next to a running k_expand
+    // (a programmatic dependent is launched only when ALL blocks of its primary have started).  The limit is
+    // set through shared memory: static (36 KB) + this unused dynamic pad + 1 KB reserved > 228 KB / 5.
+    const uint32_t per_sm = 4;
+    constexpr uint32_t kOccupancyPadBytes = 10240;
     uint32_t grid = (uint32_t)sm_count * per_sm;
     if (grid > n_tiles) grid = n_tiles;
 
@@ -886,21 +1010,37 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(kExpandThreads);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = kOccupancyPadBytes;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // overlap the launch with k_prep's tail
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    const uint32_t ov = overlap_previous ? 1u : 0u;
     if (vec)
-        return cudaLaunchKernelEx(&cfg, k_expand<true>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
-    return cudaLaunchKernelEx(&cfg, k_expand<false>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles);
+        return cudaLaunchKernelEx(&cfg, k_expand<true>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles, ov,
+                                  prep_epoch_wanted);
+    return cudaLaunchKernelEx(&cfg, k_expand<false>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles, ov,
+                              prep_epoch_wanted);
 }
 
 }  // namespace gs
 
 #ifdef GS_EXPAND_TRACE
+extern "C" int gs_debug_ktrace_reset() {
+    static unsigned long long lo[64 * 2 * 6], hi[64 * 2 * 6];
+    for (auto& v : lo) v = ~0ull;
+    for (auto& v : hi) v = 0;
+    cudaError_t e = cudaMemcpyToSymbol(gs::g_kmin, lo, sizeof lo);
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(gs::g_kmax, hi, sizeof hi);
+    return (int)e;
+}
+extern "C" int gs_debug_ktrace_read(unsigned long long* lo, unsigned long long* hi) {
+    cudaError_t e = cudaMemcpyFromSymbol(lo, gs::g_kmin, sizeof(gs::g_kmin));
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(hi, gs::g_kmax, sizeof(gs::g_kmax));
+    return (int)e;
+}
 extern "C" int gs_debug_expand_trace(unsigned long long* host, size_t n) {
     if (n > sizeof(gs::g_trace) / 8) n = sizeof(gs::g_trace) / 8;
     return (int)cudaMemcpyFromSymbol(host, gs::g_trace, n * 8);

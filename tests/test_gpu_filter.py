@@ -197,3 +197,49 @@ def test_pipelined_back_to_back_filters_are_identical():
             assert (bm == want).all(), j
             seen.add(j)
         assert seen == set(range(12))
+
+
+def test_pipelined_mixed_sizes_and_state_changes():
+    """Overlapped batches of very different sizes (grids from one CTA to several waves), each with its own output
+    buffer, enqueued back to back; half way through the first round, pod events change the snapshot (which ends
+    the chain of overlapping filters) and the batches after it must see the new state.  Every bitmap is compared
+    with the reference afterwards."""
+    import torch
+
+    sc = synth.make_config("C3")
+    cap, used, ndev, cls, _ = H.soa_state(sc)
+    key0, elig0 = S.node_keys(cap, used, ndev, cls)
+    sizes = [1, 64, 3000, 7, 2048, 65, 12288, 130, 1, 5000, 640, 3]
+    rng = np.random.default_rng(7)
+    with H.load_snapshot(sc, extra_pods=4096) as s:
+        s.set_option(gsx.capi.OPT_PIPELINE_FILTERS, 1)
+        stride = (s.bitmap_words + 7) // 8 * 8
+        st = torch.cuda.Stream()
+        batches = [synth.make_requests(n, "adversarial" if i % 3 else "catalogue", 300 + i).astype(np.uint64)
+                   for i, n in enumerate(sizes)]
+        d_reqs = [torch.from_numpy(b.view(np.int64)).cuda() for b in batches]
+        outs = [torch.full((n, stride), -1, dtype=torch.int32, device="cuda") for n in sizes]
+        # events applied between batch 5 and batch 6: fill one device of many nodes
+        n_ev = 2000
+        nodes = rng.choice(sc.n_nodes, n_ev, replace=False).astype(np.uint32)
+        ev = synth.add_events(sc.n_pods + np.arange(n_ev, dtype=np.uint32), nodes, np.zeros(n_ev, np.int16),
+                              np.full(n_ev, 150000, np.uint64))
+        torch.cuda.synchronize()
+        for rep in range(3):  # the same sequence three times: epochs and buffer sets keep alternating
+            for i, d_req in enumerate(d_reqs):
+                if rep == 0 and i == 6:
+                    st.synchronize()   # calls on one snapshot are ordered by the caller: the filters above read `used`
+                    s.pods_apply(ev)   # (synchronous on the snapshot's own stream)
+                s.filter_batch_device(d_req.data_ptr(), sizes[i], outs[i].data_ptr(), stride, st.cuda_stream)
+            st.synchronize()
+            if rep == 0:
+                first = [o.cpu().numpy().view(np.uint32).copy() for o in outs]
+        last = [o.cpu().numpy().view(np.uint32).copy() for o in outs]
+        used1 = s.read_used().reshape(used.shape)
+        key1, elig1 = S.node_keys(cap, used1, ndev, cls)
+        assert (key1 != key0).any()
+        for i in range(len(sizes)):
+            before = S.pack_bitmap(S.filter_pass(batches[i], key0, elig0), stride)
+            after = S.pack_bitmap(S.filter_pass(batches[i], key1, elig1), stride)
+            assert (first[i] == (before if i < 6 else after)).all(), ("first pass", i)
+            assert (last[i] == after).all(), ("last pass", i)

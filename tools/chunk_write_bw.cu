@@ -61,6 +61,12 @@ __global__ void k_tile3(uint4* out, int n_rows, int pitch16, int cb_count, int s
     if (cols16 == 0) cols16 = pitch16;
     __shared__ unsigned s_tile;
     __shared__ unsigned long long s_off[64];
+    __shared__ unsigned s_big[(MODE & 128) ? 9000 : 1];
+    if (MODE & 128) s_big[threadIdx.x] = threadIdx.x;
+    if (MODE & 64) {
+        if (!(MODE & 256)) asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    }
     int n_tiles = (n_rows / tile_rows) * cb_count;
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     int t = blockIdx.x;
@@ -95,6 +101,19 @@ __global__ void k_tile3(uint4* out, int n_rows, int pitch16, int cb_count, int s
     if ((MODE & 2) && threadIdx.x == 0) {
         __threadfence();
         if (atomicAdd(&sched[1], 1u) == gridDim.x - 1) { sched[0] = 0; sched[1] = 0; }
+    }
+    if (MODE & 256) asm volatile("griddepcontrol.wait;" ::: "memory");  // complete only after the predecessor
+}
+// a small kernel between two big ones, as k_prep sits between two k_expand launches
+template <int WAIT_AT_END>
+__global__ void k_mid(unsigned* ctr, int spin_ns) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (threadIdx.x == 0) {
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+        do { asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1)); } while (t1 - t0 < (unsigned long long)spin_ns);
+        atomicAdd(ctr, 1u);
+        if (WAIT_AT_END) asm volatile("griddepcontrol.wait;" ::: "memory");
     }
 }
 int main() {
@@ -138,6 +157,56 @@ int main() {
     for (auto& b : buf) { cudaFree(b); cudaMalloc(&b, (size_t)10048 * 6400); }
 #define RUN4(M) run("pitch 6400: k_tile3 mode " #M, [&](uint4* o) { k_tile3<M><<<740, 256>>>(o, rows, 400, 13, 32, 64, sched, aux, 391); });
     RUN4(0) RUN4(32) RUN4(9) RUN4(2) RUN4(11) RUN4(43)
+    unsigned* sched2; cudaMalloc(&sched2, 64); cudaMemset(sched2, 0, 64);
+    int flip = 0;
+    int grid2 = 740;
+    auto pdl2 = [&](auto kern, uint4* o) {  // consecutive launches overlap: each has its own ticket counter
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid2); cfg.blockDim = dim3(256);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        flip = (flip + 1) % 3;
+        cudaLaunchKernelEx(&cfg, kern, o, rows, 400, 13, 32, 64, sched2 + 4 * flip, (const unsigned*)aux, 392);
+    };
+    auto pdl = [&](auto kern, uint4* o) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(740); cfg.blockDim = dim3(256);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, kern, o, rows, 400, 13, 32, 64, sched, (const unsigned*)aux, 392);
+    };
+    run("pitch 6400/392: static", [&](uint4* o) { k_tile3<0><<<740, 256>>>(o, rows, 400, 13, 32, 64, sched, aux, 392); });
+    run("pitch 6400/392: static + 36KB smem", [&](uint4* o) { k_tile3<128><<<740, 256>>>(o, rows, 400, 13, 32, 64, sched, aux, 392); });
+    run("pitch 6400/392: static + PDL", [&](uint4* o) { pdl(k_tile3<64>, o); });
+    run("pitch 6400/392: static + PDL + smem", [&](uint4* o) { pdl(k_tile3<64 + 128>, o); });
+    run("pitch 6400/392: tickets", [&](uint4* o) { k_tile3<2><<<740, 256>>>(o, rows, 400, 13, 32, 64, sched, aux, 392); });
+    run("pitch 6400/392: tickets + PDL + smem", [&](uint4* o) { pdl(k_tile3<2 + 64 + 128>, o); });
+    run("pitch 6400/392: tickets + PDL overlapped", [&](uint4* o) { pdl2(k_tile3<2 + 64 + 256>, o); });
+    run("pitch 6400/392: tickets + PDL overlapped + smem", [&](uint4* o) { pdl2(k_tile3<2 + 64 + 128 + 256>, o); });
+    unsigned* ctr; cudaMalloc(&ctr, 4); cudaMemset(ctr, 0, 4);
+    auto mid = [&](auto kern, int blocks) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(128);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, kern, ctr, 2000);
+    };
+    run("overlapped + mid kernel 148 blocks", [&](uint4* o) { mid(k_mid<0>, 148); pdl2(k_tile3<2 + 64 + 128 + 256>, o); });
+    run("overlapped + mid kernel 470 blocks", [&](uint4* o) { mid(k_mid<0>, 470); pdl2(k_tile3<2 + 64 + 128 + 256>, o); });
+    run("overlapped + mid kernel 470, wait at end", [&](uint4* o) { mid(k_mid<1>, 470); pdl2(k_tile3<2 + 64 + 128 + 256>, o); });
+    for (int g : {592, 444, 296}) {
+        grid2 = g;
+        char name[96];
+        snprintf(name, sizeof name, "overlapped, grid %d", g);
+        run(name, [&](uint4* o) { pdl2(k_tile3<2 + 64 + 128 + 256>, o); });
+    }
+    grid2 = 740;
     // row pitch sweep, 391 x 16 B used per row, static round-robin tiles of 64 rows x 512 B
     for (auto& b : buf) { cudaFree(b); cudaMalloc(&b, (size_t)10048 * 8192); }
     for (int p16 : {391, 392, 394, 396, 400, 404, 408, 416, 424, 448, 512}) {
