@@ -274,8 +274,7 @@ def run_product(args):
     # of ONE stage (same inputs, same rotating outputs); the stages of a step sum to ~ms_per_step
     kernel_ms = {}
     for name, mask in (("prep_pods", gsx.capi.STAGE_SORT), ("prep_nodes", gsx.capi.STAGE_NODE_RANK),
-                       ("prep", gsx.capi.STAGE_SORT | gsx.capi.STAGE_NODE_RANK), ("settle", gsx.capi.STAGE_SETTLE),
-                       ("expand", gsx.capi.STAGE_EXPAND)):
+                       ("prep", gsx.capi.STAGE_SORT | gsx.capi.STAGE_NODE_RANK), ("expand", gsx.capi.STAGE_EXPAND)):
         for i in range(3):
             snap.filter_stages_device(mask, d_req.data_ptr(), P, outs[i % N_OUT_BUFFERS].data_ptr(), stride, stream)
         torch.cuda.synchronize()

@@ -12,7 +12,7 @@ LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libgpushare_b200.so")
 
 SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu", "noalloc.cu", "ext.cpp"]
-HEADERS = ["common.cuh", "kernels.h", "exports.map", "ext_state.inc", "ext_handlers.inc", "tile_kernels.inc",
+HEADERS = ["common.cuh", "kernels.h", "exports.map", "ext_state.inc", "ext_handlers.inc",
            os.path.join(ROOT, "include", "gpushare_ext.h"), os.path.join(ROOT, "include", "gpushare_b200.h")]
 
 NVCC_FLAGS = [

@@ -18,10 +18,10 @@ EV_ADD, EV_REMOVE = 0, 1
 POD_VALID, POD_COUNTED = 1, 2
 BIND_NO_DEVICE, BIND_NODE_NOT_FOUND = -1, -2
 MAX_DEVS, MAX_BATCH = 64, 12288
-STAGE_SORT, STAGE_NODE_RANK, STAGE_EXPAND, STAGE_SETTLE, STAGE_ALL = 1, 2, 4, 8, 15
+STAGE_SORT, STAGE_NODE_RANK, STAGE_EXPAND = 1, 2, 4
 OPT_PIPELINE_FILTERS = 1
-K_REBUILD, K_APPLY, K_SORT, K_NODE_RANK, K_EXPAND, K_BIND_SORT, K_BIND_SCAN, K_SETTLE = range(8)
-KERNEL_NAMES = ["rebuild", "apply", "sort", "node_rank", "expand", "bind_sort", "bind_scan", "settle"]
+K_REBUILD, K_APPLY, K_SORT, K_NODE_RANK, K_EXPAND, K_BIND_SORT, K_BIND_SCAN = range(7)
+KERNEL_NAMES = ["rebuild", "apply", "sort", "node_rank", "expand", "bind_sort", "bind_scan"]
 
 # numpy mirrors of the C structs (layouts asserted against sizeof in tests/test_abi.py)
 NODE_DT = np.dtype([("dev_capacity", "<u8"), ("node_idx", "<u4"), ("dev_count", "<u4"),

@@ -143,7 +143,7 @@ uint32_t bitmap_words(const gs_snapshot* s) { return (s->n_nodes + 31u) / 32u; }
 
 // The three filter kernels for one chunk of <= GS_MAX_BATCH pods; everything on `st`.
 int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_out, uint32_t row_stride,
-                 cudaStream_t st, uint32_t stages = GS_STAGE_ALL) {
+                 cudaStream_t st, uint32_t stages = 7u) {
     const uint32_t words = bitmap_words(s);
     if (n_pods == 0 || words == 0) return GS_OK;
     const uint32_t words_pad = (words + gs::kTileWords - 1) / gs::kTileWords * gs::kTileWords;
@@ -152,7 +152,7 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     // full launches alternate; single-stage profiling launches stay on one set (development builds can let
     // expand-only launches alternate and overlap too: GS_EXPAND_TRACE + option value 2)
     const bool dev_overlap_expand = s->pipeline_dev && stages == GS_STAGE_EXPAND;
-    if (stages == GS_STAGE_ALL || dev_overlap_expand) s->fb_set ^= 1u;
+    if (stages == 7u || dev_overlap_expand) s->fb_set ^= 1u;
     gs::FilterBuffers fb;
     fb.grouped_req = s->d_sorted_keys + (size_t)set * GS_MAX_BATCH;
     fb.perm = s->d_perm + (size_t)set * GS_MAX_BATCH;
@@ -163,20 +163,16 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     fb.node_key32 = s->d_node_key32 + (size_t)set * s->rank_words * 32;
     fb.sched = s->d_sched + set * 2;
     fb.set_index = set;
-    fb.prep_done = s->d_epochs + 8 * set;
-    fb.prep_epoch = s->d_epochs + 8 * set + 1;
-    fb.expand_epoch = s->d_epochs + 8 * set + 2;
-    fb.settle_done = s->d_epochs + 8 * set + 3;
-    fb.settle_epoch = s->d_epochs + 8 * set + 4;
-    fb.records = reinterpret_cast<gs::TileRecord*>(static_cast<char*>(s->d_tile_records) + (size_t)set * s->max_tiles * gs::tile_record_bytes());
-    fb.payloads = reinterpret_cast<gs::TilePayload*>(static_cast<char*>(s->d_tile_payloads) + (size_t)set * s->max_tiles * gs::tile_payload_bytes());
+    fb.prep_done = s->d_epochs + 3 * set;
+    fb.prep_epoch = s->d_epochs + 3 * set + 1;
+    fb.expand_epoch = s->d_epochs + 3 * set + 2;
     // With GS_OPT_PIPELINE_FILTERS, a filter that directly follows another filter of this snapshot on the same
     // stream, writing somewhere else, does not wait for that filter's expand kernel to drain before its own prep
     // kernel starts (the two touch different work-buffer sets).  Anything else keeps plain stream order.
     const char* out_lo = reinterpret_cast<const char*>(d_out);
     const char* out_hi = out_lo + (size_t)n_pods * row_stride * sizeof(uint32_t);
     const bool overlap_ok = dev_overlap_expand ||
-                            (s->pipeline && stages == GS_STAGE_ALL && s->prev_filter && s->prev_stream == st &&
+                            (s->pipeline && stages == 7u && s->prev_filter && s->prev_stream == st &&
                              (out_hi <= s->prev_out_lo || out_lo >= s->prev_out_hi));
     // bucket scale: requests up to the largest device capacity spread over all 512 buckets
     uint32_t bits = 0;
@@ -192,20 +188,15 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
             return e;
         });
     if (rc) return rc;
-    if (stages & GS_STAGE_SETTLE)
-        rc = timed(s, GS_K_SETTLE, st, 1, [&] {
-            cudaError_t e = gs::launch_settle(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, s->n_prep[set], st);
-            if (e == cudaSuccess) ++s->n_settle[set];
-            return e;
-        });
-    if (rc) return rc;
     if (stages & GS_STAGE_EXPAND)
-        rc = timed(s, GS_K_EXPAND, st, 1, [&] {
-            cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, s->n_settle[set], st);
-            if (e == cudaSuccess) ++s->n_expand[set];
-            return e;
-        });
-    s->prev_filter = rc == GS_OK && stages == GS_STAGE_ALL && !s->profiling;
+        rc = timed(s, GS_K_EXPAND, st, 1,
+                   [&] {
+                       cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok,
+                                                         s->n_prep[set], st);
+                       if (e == cudaSuccess) ++s->n_expand[set];
+                       return e;
+                   });
+    s->prev_filter = rc == GS_OK && stages == 7u && !s->profiling;
     s->prev_stream = st;
     s->prev_out_lo = out_lo;
     s->prev_out_hi = out_hi;
@@ -288,11 +279,8 @@ int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32
     CU_NEW(cudaMalloc(&s->d_row_bucket, 2 * (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
     CU_NEW(cudaMalloc(&s->d_pod_hist, 516 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 516 * sizeof(uint32_t), s->stream));
-    CU_NEW(cudaMalloc(&s->d_epochs, 16 * sizeof(uint32_t)));
-    CU_NEW(cudaMemsetAsync(s->d_epochs, 0, 16 * sizeof(uint32_t), s->stream));
-    s->max_tiles = (size_t)(GS_MAX_BATCH / gs::kTileRows) * (s->rank_words / gs::kTileWords);
-    CU_NEW(cudaMalloc(&s->d_tile_records, 2 * s->max_tiles * gs::tile_record_bytes()));
-    CU_NEW(cudaMalloc(&s->d_tile_payloads, 2 * s->max_tiles * gs::tile_payload_bytes()));
+    CU_NEW(cudaMalloc(&s->d_epochs, 6 * sizeof(uint32_t)));
+    CU_NEW(cudaMemsetAsync(s->d_epochs, 0, 6 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMalloc(&s->d_sched, 4 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_sched, 0, 4 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMemsetAsync(s->d_used, 0, (size_t)max_nodes * max_devs * sizeof(u64), s->stream));
@@ -326,8 +314,6 @@ int gs_snapshot_destroy(gs_snapshot* s) {
     cudaFree(s->d_pod_hist);
     cudaFree(s->d_sched);
     cudaFree(s->d_epochs);
-    cudaFree(s->d_tile_records);
-    cudaFree(s->d_tile_payloads);
     cudaFree(s->d_stage);
     cudaFree(s->d_bitmap);
     if (s->h_stage) cudaFreeHost(s->h_stage);

@@ -60,14 +60,9 @@ struct gs_snapshot {
     // launches alternate between them, so that with GS_OPT_PIPELINE_FILTERS the prep kernel of one batch can run
     // under the tail of the previous batch's expand kernel.
     uint32_t fb_set = 0;
-    uint32_t* d_epochs = nullptr;     // per set s, at [8 * s]: finished k_prep blocks, k_prep epoch, k_expand epoch,
-                                      // finished k_settle CTAs, k_settle epoch
-    uint32_t n_prep[2] = {0, 0};      // k_prep / k_settle / k_expand launches issued per set (what the epochs will reach)
-    uint32_t n_settle[2] = {0, 0};
+    uint32_t* d_epochs = nullptr;     // per set s: [3 * s] finished k_prep blocks, [3 * s + 1] k_prep epoch, [3 * s + 2] k_expand epoch
+    uint32_t n_prep[2] = {0, 0};      // k_prep / k_expand launches issued per set (what the epochs will reach)
     uint32_t n_expand[2] = {0, 0};
-    void* d_tile_records = nullptr;   // [2 sets][max row tiles x column blocks] TileRecord (K3)
-    void* d_tile_payloads = nullptr;  // [2 sets][max row tiles x column blocks] TilePayload (K3)
-    size_t max_tiles = 0;
     bool pipeline = false;            // GS_OPT_PIPELINE_FILTERS
     bool pipeline_dev = false;        // development builds: expand-only launches overlap as well
     bool prev_filter = false;         // the last operation enqueued for this snapshot was a filter ...

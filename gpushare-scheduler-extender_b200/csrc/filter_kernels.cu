@@ -216,10 +216,10 @@ k_radix_sort(Loader load_key, uint32_t n, u64* __restrict__ out_keys, uint16_t* 
 // key < all of them.  q' is written bit-sliced, plane-major inside blocks of kTileWords words:
 //   planes[((word / kTileWords) * kRankPlanes + k) * kTileWords + word % kTileWords] = bit k of 32 q'.
 #ifdef GS_EXPAND_TRACE
-// development builds only: per launch (ring of 64), per kernel (0 = k_prep, 1 = k_expand, 2 = k_settle), earliest / latest
+// development builds only: per launch (ring of 64), per kernel (0 = k_prep, 1 = k_expand), earliest / latest
 // globaltimer of: 0 block entry, 1 past the start wait, 2 block exit (tools/overlap_trace.py)
-__device__ unsigned long long g_kmin[64][3][6];
-__device__ unsigned long long g_kmax[64][3][6];
+__device__ unsigned long long g_kmin[64][2][6];
+__device__ unsigned long long g_kmax[64][2][6];
 __device__ __forceinline__ void ktrace(uint32_t seq, int kernel, int what) {
     unsigned long long gt;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
@@ -429,7 +429,476 @@ __device__ __forceinline__ uint32_t planes_ge(const uint32_t (&a)[kRankPlanes], 
     return ge;
 }
 
-#include "tile_kernels.inc"
+// A tile is kTileRows consecutive grouped pods x kTileWords words (4096 nodes); its rows span request
+// buckets [bmin, bmax].  A node with q' > bmax passes in every row (base word), one with q' < bmin in
+// none; only nodes with bmin <= q' <= bmax need the exact comparison key >= req per row.  Words holding
+// such nodes ("partial" words) are settled per tile in one of two ways:
+//   sparse tile (<= kSparseCap partial words, each with <= kSparseMax compared nodes): lane = row, exact
+//     compares against the few keys, results in a small shared-memory patch;
+//   dense tile (anything else): the tile's rows are sorted, every node of a partial word gets
+//     cnt = #{rows : req <= key} by binary search (lane = node), and row i of the sorted tile has the
+//     node's bit set iff cnt > i; the counts are kept bit-sliced.
+// Every other word goes from registers straight to global memory.  Stores are 16 bytes per lane, 512
+// contiguous bytes per warp and row.  (Bulk asynchronous stores of 512-byte row segments from a
+// shared-memory tile were measured slower than this: profiles/NOTES.md.)
+//
+// Node keys reach shared memory only through bulk asynchronous copies: an ordinary load issued by an SM
+// that is streaming stores waits behind them for microseconds (profiles/NOTES.md), and so does everything
+// that depends on it.  The copies are issued as soon as the tile is classified, and the lanes whose four
+// words are the same in every row store all their rows while the keys are in flight.
+//
+// Keys are compared as 32-bit saturated values (node_key32 = min(key, 2^32 - 1)), which is exact for every
+// request below 2^32; a tile holding a larger request (a wrapped negative sum, pkg/cache/nodeinfo.go:217)
+// is a "wide" tile and takes the dense path over the full 64-bit keys, half a tile of keys at a time.
+constexpr int kSparseMax = 4;       // compared nodes per word on the lane = row path
+constexpr uint32_t kSparseCap = 16; // partial words per tile on that path
+constexpr uint32_t kPatchStride = kTileRows + 1;  // odd: phase D reads one row of several patched words
+constexpr uint32_t kStageWords = 4096;            // 16 KB: the tile's 4096 32-bit keys, or 2048 64-bit ones
+
+struct ExpandSmem {
+    // dense tile: node keys; sparse tile: [kSparseCap][32] keys, then [kSparseCap][kPatchStride] patch
+    uint32_t stage[kStageWords];
+    u64 req[kTileRows];                 // requests of the tile's rows (~0 beyond the last row)
+    u64 req_sorted[kTileRows];          // the same in ascending order (dense tiles)
+    u64 off_sorted[kTileRows];
+    u64 row_off[kTileRows];             // word offset of every tile row's output row (pod index x row stride)
+    uint32_t basew[kTileWords];         // nodes passing in every row
+    uint32_t somew[kTileWords];         // nodes that can pass in some row (q' >= bmin)
+    uint32_t pmask[kTileWords];         // nodes that need the comparison (some & ~base)
+    uint32_t cntp[kTileWords * 8];      // dense tiles: per-node pass counts (0..64), bit-sliced, 7 planes used
+    uint8_t plist[kTileWords];          // the partial words
+    uint8_t pidx[kTileWords];           // position in plist, 0xff = the word is the same in every row
+    uint32_t n_partial, n_heavy, next_tile;
+};
+constexpr uint32_t kSparseKeyWords = kSparseCap * 32;
+static_assert(kSparseKeyWords + kSparseCap * kPatchStride <= kStageWords, "sparse keys + patch share the stage");
+
+// Inputs of one tile, brought in by bulk asynchronous copies (TMA) that complete on an mbarrier, one tile
+// ahead.
+constexpr int kPrefetch = 2;
+struct __align__(128) TileInputs {
+    uint32_t planes[kRankPlanes * kTileWords];  // bucket-id planes of the tile's 128 words
+    u64 req[kTileRows];                         // requests of the tile's rows
+    uint16_t perm[kTileRows];                   // their pod indices
+    uint16_t bucket[kTileRows];                 // their 1-based buckets
+};
+constexpr uint32_t kTileInputBytes = sizeof(TileInputs);
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(sdst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// orders this thread's earlier generic-proxy accesses to shared memory before its later asynchronous copies
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+#ifdef GS_EXPAND_TRACE
+// development builds only: per CTA and tile, SM cycle stamps of the phases (tools/expand_trace.py)
+constexpr int kTraceTiles = 6, kTraceSlots = 12;
+__device__ unsigned long long g_trace[148 * 5 * kTraceTiles * kTraceSlots];
+#define GS_TRACE(slot) \
+    do { if (tid == 0 && it < kTraceTiles) g_trace[((size_t)blockIdx.x * kTraceTiles + it) * kTraceSlots + (slot)] = clock64(); } while (0)
+#define GS_TRACE_VAL(slot, v) \
+    do { if (tid == 0 && it < kTraceTiles) g_trace[((size_t)blockIdx.x * kTraceTiles + it) * kTraceSlots + (slot)] = (v); } while (0)
+#else
+#define GS_TRACE(slot) do {} while (0)
+#define GS_TRACE_VAL(slot, v) do {} while (0)
+#endif
+
+template <bool kVec>
+__global__ void __launch_bounds__(kExpandThreads, 5)
+k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_stride, uint32_t* __restrict__ out,
+         uint32_t n_col_blocks, uint32_t inv_col_blocks, uint32_t n_tiles, uint32_t overlap_previous,
+         uint32_t prep_epoch_wanted) {
+    __shared__ __align__(128) ExpandSmem sm;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr uint32_t kWarps = kExpandThreads / 32;
+    static_assert(kExpandThreads >= kTileWords + kTileRows, "phase A: one thread per word, one per row");
+    const uint32_t* __restrict__ planes = fb.planes;
+
+    __shared__ TileInputs tin[kPrefetch];
+    __shared__ __align__(8) uint64_t tin_bar[kPrefetch];
+    __shared__ __align__(8) uint64_t key_bar;  // completion of the key copies of the current tile
+    uint32_t key_phase = 0;
+
+    // thread 0: request the inputs of the tile with ticket `ticket_no` into stage `stage`
+    auto request = [&](uint32_t ticket_no, uint32_t stage) {
+        if (ticket_no >= n_tiles) return;
+        const uint32_t t = n_tiles - 1u - ticket_no;  // high buckets first: that is where node keys cluster
+        const uint32_t rt = inv_col_blocks ? __umulhi(t, inv_col_blocks) : t, cb = t - rt * n_col_blocks;  // t / n_col_blocks
+        const uint32_t j0 = rt * kTileRows;
+        TileInputs& in = tin[stage];
+        mbar_expect_tx(&tin_bar[stage], kTileInputBytes);
+        bulk_load(in.planes, planes + (size_t)cb * kRankPlanes * kTileWords, sizeof(in.planes), &tin_bar[stage]);
+        bulk_load(in.req, fb.grouped_req + j0, sizeof(in.req), &tin_bar[stage]);
+        bulk_load(in.perm, fb.perm + j0, sizeof(in.perm), &tin_bar[stage]);
+        bulk_load(in.bucket, fb.row_bucket + j0, sizeof(in.bucket), &tin_bar[stage]);
+    };
+
+    // Tile schedule: the first tile of a CTA is blockIdx.x; every later one is a ticket taken during the
+    // current tile (after its dense work, if any), so a CTA never holds more than one tile ahead and
+    // CTAs stuck in a dense tile simply take fewer.  (Tickets taken two tiles ahead hide the ticket's round
+    // trip but hoard: an isolated launch went from 17.6 to 20.2 us; profiles/NOTES.md.)
+    uint32_t ticket = 0;  // thread 0
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < kPrefetch; ++i) mbar_init(&tin_bar[i], 1);
+        mbar_init(&key_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        sm.n_partial = 0;
+        sm.n_heavy = 0;
+    }
+    // Everything above overlapped the tail of k_prep; its results are needed from here on.  Normally this
+    // grid waits for all earlier work in the stream.  When the host knows that the work before this batch's
+    // k_prep is the expand kernel of another batch (other work buffers, other output), this grid only waits for
+    // its own k_prep, by epoch, and so fills the SM slots that the previous expand kernel frees one by one
+    // instead of idling through its tail.  A following grid is let in after that point.
+    GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 0);
+    if (!overlap_previous) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    } else {
+        if (tid == 0) {
+            wait_epoch(fb.prep_epoch, prep_epoch_wanted);
+            asm volatile("fence.proxy.async;" ::: "memory");  // the bulk copies below read what k_prep wrote
+        }
+        __syncthreads();
+    }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 1);
+    if (tid == 0) request(blockIdx.x, 0);
+    __syncthreads();
+    uint32_t cur = blockIdx.x;
+
+    for (uint32_t it = 0; cur < n_tiles; ++it) {
+        const uint32_t stage = it % kPrefetch, parity = (it / kPrefetch) & 1u;
+        const uint32_t tile = n_tiles - 1u - cur;
+        const uint32_t rt = inv_col_blocks ? __umulhi(tile, inv_col_blocks) : tile, cb = tile - rt * n_col_blocks;
+        const uint32_t j0 = rt * kTileRows;
+        const uint32_t rows = min((uint32_t)kTileRows, n_pods - j0);
+        const uint32_t w0 = cb * kTileWords;
+        const TileInputs& in = tin[stage];
+        GS_TRACE(0);
+        mbar_wait(&tin_bar[stage], parity);
+        GS_TRACE(1);
+
+        // A: one thread per word (threads 0..127), one per row (threads 128..191)
+        uint32_t my_pi = 0xffu;  // threads 0..127: position of the thread's word among the partial ones
+        int big_req = 0;         // threads 128..191: the row's request does not fit 32 bits
+        if (tid < kTileWords) {
+            uint32_t a[kRankPlanes];
+#pragma unroll
+            for (int k = 0; k < kRankPlanes; ++k) a[k] = in.planes[k * kTileWords + tid];
+            const uint32_t bmin = in.bucket[0], bmax = in.bucket[rows - 1];
+            // the last bucket is open-ended: no node is known to cover all of it
+            const uint32_t t_all = bmax == kBuckets ? kBuckets + 2u : bmax + 1u;
+            const uint32_t all_rows = planes_ge(a, t_all);
+            const uint32_t some_rows = planes_ge(a, bmin);
+            const uint32_t pm = some_rows & ~all_rows;
+            sm.basew[tid] = all_rows;
+            sm.somew[tid] = some_rows;
+            sm.pmask[tid] = pm;
+            if (pm) {
+                my_pi = atomicAdd(&sm.n_partial, 1u);
+                sm.plist[my_pi] = (uint8_t)tid;
+                if (__popc(pm) > kSparseMax) sm.n_heavy = 1u;
+            }
+            sm.pidx[tid] = (uint8_t)my_pi;
+        } else if (tid < kTileWords + kTileRows) {
+            const uint32_t r = tid - kTileWords;
+            const uint32_t row = (uint32_t)in.perm[r];
+            const u64 rq = in.req[r];
+            sm.row_off[r] = (u64)row * row_stride;
+            sm.req[r] = r < rows ? rq : ~0ull;
+            big_req = (r < rows && (rq >> 32) != 0) ? 1 : 0;
+        }
+        // phase A results are visible; nobody reads this stage's inputs any more
+        const bool wide = __syncthreads_or(big_req) != 0;
+
+        const uint32_t np = sm.n_partial;
+        const bool dense = np != 0 && (sm.n_heavy != 0 || np > kSparseCap || wide);
+        const bool sparse = np != 0 && !dense;
+        GS_TRACE(2);
+        GS_TRACE_VAL(8, (unsigned long long)np | ((unsigned long long)dense << 16) | ((unsigned long long)wide << 17) | ((unsigned long long)tile << 32));
+        {
+            unsigned long long gt;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
+            GS_TRACE_VAL(9, gt);
+        }
+
+        // the keys this tile needs, on their way while the rows that do not need them are stored
+        u64* const stage64 = reinterpret_cast<u64*>(sm.stage);
+        if (dense) {
+            if (tid == 0) {
+                fence_async_smem();
+                mbar_expect_tx(&key_bar, kStageWords * 4u);
+                if (wide)  // the keys of the first 64 words
+                    bulk_load(stage64, fb.node_key + (size_t)w0 * 32, kStageWords * 4u, &key_bar);
+                else
+                    bulk_load(sm.stage, fb.node_key32 + (size_t)w0 * 32, kStageWords * 4u, &key_bar);
+            }
+        } else if (sparse) {
+            // each partial word's thread fetches the 32 keys of its word (128 bytes); the expected byte count
+            // may be posted after some of the copies have already landed, which the barrier allows
+            if (tid == 0) mbar_expect_tx(&key_bar, np * 128u);
+            if (my_pi != 0xffu) {
+                fence_async_smem();
+                bulk_load(&sm.stage[my_pi * 32], fb.node_key32 + (size_t)(w0 + tid) * 32, 128u, &key_bar);
+            }
+        }
+
+        if (!dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);  // consumed just before the stores
+
+        // Dense tiles want the tile's rows in ascending request order: then a node's column is a prefix of
+        // ones and one binary search per node replaces a comparison per row.
+        if (dense && tid < kTileRows) {
+            const u64 mine = sm.req[tid];
+            uint32_t rank = 0;
+#pragma unroll 8
+            for (uint32_t o = 0; o < kTileRows; ++o) {
+                const u64 other = sm.req[o];
+                rank += (other < mine || (other == mine && o < tid)) ? 1u : 0u;
+            }
+            sm.req_sorted[rank] = mine;
+            sm.off_sorted[rank] = sm.row_off[tid];
+        }
+        GS_TRACE(3);
+
+        if (!dense && tid == 0) {  // the next tile is known: start fetching its inputs
+            sm.next_tile = gridDim.x + ticket;
+            request(sm.next_tile, stage ^ 1u);
+        }
+        // D, first part: lane owns 4 words, warp owns rows warp, warp + kWarps, ...; 16 bytes per lane, 512
+        // contiguous bytes per warp and row.  Lanes whose four words are the same in every row store now.
+        const uint32_t wcol = w0 + lane * 4;
+        uint4 b4 = make_uint4(0, 0, 0, 0);
+        uint32_t p4 = 0xffffffffu;
+        if (kVec) {
+            b4 = *reinterpret_cast<const uint4*>(&sm.basew[lane * 4]);
+            p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lane * 4]);
+            if (wcol < words_out && p4 == 0xffffffffu) {
+                uint32_t* dst = out + wcol;
+#pragma unroll 4
+                for (uint32_t rr = warp; rr < rows; rr += kWarps)
+                    __stcs(reinterpret_cast<uint4*>(dst + sm.row_off[rr]), b4);
+            }
+        } else {
+            for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                uint32_t* dst = out + sm.row_off[rr] + w0;
+#pragma unroll
+                for (int c = 0; c < kTileWords / 32; ++c) {
+                    const uint32_t wl = c * 32 + lane;
+                    if (w0 + wl < words_out && sm.pidx[wl] == 0xffu) __stcs(dst + wl, sm.basew[wl]);
+                }
+            }
+        }
+
+        if (np) {  // uniform
+            GS_TRACE(4);
+            if (dense) {
+                // per node of every partial word: cnt = #{rows : req <= key}, kept bit-sliced (plane-major)
+                __syncthreads();  // req_sorted is complete
+                GS_TRACE(10);
+                const uint32_t passes = wide ? 2u : 1u;
+                for (uint32_t pass = 0; pass < passes; ++pass) {
+                    if (pass && tid == 0) {  // wide tile: the keys of words 64..127 replace those of 0..63
+                        fence_async_smem();
+                        mbar_expect_tx(&key_bar, kStageWords * 4u);
+                        bulk_load(stage64, fb.node_key + (size_t)(w0 + 64u) * 32, kStageWords * 4u, &key_bar);
+                    }
+                    mbar_wait(&key_bar, key_phase);
+                    key_phase ^= 1u;
+                    GS_TRACE(11);
+                    // each warp owns partial words warp, warp + 8, ... and runs four of them at a time, so
+                    // that four independent binary searches hide each other's shared-memory latency
+                    for (uint32_t k0 = warp; k0 < np; k0 += 4 * kWarps) {
+                        uint32_t cnt[4], t[4];
+                        u64 key[4];
+                        bool on[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const uint32_t k = k0 + u * kWarps;
+                            t[u] = k < np ? sm.plist[k] : 0u;
+                            on[u] = k < np && (!wide || (t[u] >> 6) == pass);  // warp-uniform
+                            key[u] = 0ull;
+                            if (on[u]) key[u] = wide ? stage64[(t[u] & 63u) * 32 + lane] : (u64)sm.stage[t[u] * 32 + lane];
+                            cnt[u] = 0;
+                        }
+                        // branch-free upper bound over the 64 sorted requests
+#pragma unroll
+                        for (uint32_t step = kTileRows / 2; step > 0; step >>= 1) {
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                if (sm.req_sorted[cnt[u] + step - 1] <= key[u]) cnt[u] += step;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (!on[u]) continue;
+                            uint32_t c = cnt[u];
+                            if (c == kTileRows - 1 && sm.req_sorted[kTileRows - 1] <= key[u]) c = kTileRows;
+                            c = min(c, rows);  // a key of ~0 also matches the padding rows
+                            // nodes outside `some` never pass (q' == 0 stores key 0, which would match a zero request)
+                            if (!((sm.somew[t[u]] >> lane) & 1u)) c = 0;
+                            uint32_t mine = 0;
+#pragma unroll
+                            for (int q = 0; q < 7; ++q) {
+                                const uint32_t bal = __ballot_sync(0xffffffffu, (c >> q) & 1u);
+                                if ((int)lane == q) mine = bal;
+                            }
+                            if (lane < 7) sm.cntp[lane * kTileWords + t[u]] = mine;
+                        }
+                    }
+                    __syncthreads();  // counts complete; the key area may be overwritten
+                }
+                if (tid == 0) {  // the ticket of a dense tile is taken late: see the schedule note above
+                    ticket = atomicAdd(&fb.sched[0], 1u);
+                    sm.next_tile = gridDim.x + ticket;
+                    request(sm.next_tile, stage ^ 1u);
+                }
+            } else {
+                // C: lane = row; the compared nodes' keys come from the staged 32 keys of the word
+                mbar_wait(&key_bar, key_phase);
+                key_phase ^= 1u;
+                uint32_t* const patch = sm.stage + kSparseKeyWords;
+                for (uint32_t k = warp; k < np; k += kWarps) {
+                    const uint32_t t = sm.plist[k];
+                    const uint32_t base = sm.basew[t];
+                    uint32_t pm = sm.pmask[t];
+                    u64 kk[kSparseMax];
+                    uint32_t kb[kSparseMax];
+#pragma unroll
+                    for (int i = 0; i < kSparseMax; ++i) {
+                        kk[i] = 0;
+                        kb[i] = 0;  // unused slots set nothing
+                        if (pm) {
+                            const uint32_t bit = __ffs(pm) - 1;
+                            pm &= pm - 1;
+                            kk[i] = sm.stage[k * 32 + bit];
+                            kb[i] = 1u << bit;
+                        }
+                    }
+                    for (uint32_t rr = lane; rr < rows; rr += 32) {
+                        const u64 rq = sm.req[rr];
+                        uint32_t v = base;
+#pragma unroll
+                        for (int i = 0; i < kSparseMax; ++i)
+                            if (kk[i] >= rq) v |= kb[i];
+                        patch[k * kPatchStride + rr] = v;
+                    }
+                }
+                __syncthreads();
+            }
+
+            // D, second part: the lanes that own a partial word
+            GS_TRACE(5);
+            const uint32_t* const patch = sm.stage + kSparseKeyWords;
+            const u64* __restrict__ toff = dense ? sm.off_sorted : sm.row_off;
+            if (kVec) {
+                if (wcol < words_out && p4 != 0xffffffffu) {
+                    uint32_t* dst = out + wcol;
+                    const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
+                    if (dense) {
+                        for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                            // bit set iff the node's pass count reaches (sorted) row + 1
+                            const uint32_t thr = rr + 1;
+                            uint4 ge = make_uint4(~0u, ~0u, ~0u, ~0u);
+#pragma unroll
+                            for (int q = 0; q < 7; ++q) {
+                                const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lane * 4]);
+                                if ((thr >> q) & 1u) {
+                                    ge.x &= pl.x; ge.y &= pl.y; ge.z &= pl.z; ge.w &= pl.w;
+                                } else {
+                                    ge.x |= pl.x; ge.y |= pl.y; ge.z |= pl.z; ge.w |= pl.w;
+                                }
+                            }
+                            uint4 v = b4;
+                            if (k0 != 0xffu) v.x = ge.x;
+                            if (k1 != 0xffu) v.y = ge.y;
+                            if (k2 != 0xffu) v.z = ge.z;
+                            if (k3 != 0xffu) v.w = ge.w;
+                            __stcs(reinterpret_cast<uint4*>(dst + toff[rr]), v);
+                        }
+                    } else {
+                        for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                            uint4 v = b4;
+                            if (k0 != 0xffu) v.x = patch[k0 * kPatchStride + rr];
+                            if (k1 != 0xffu) v.y = patch[k1 * kPatchStride + rr];
+                            if (k2 != 0xffu) v.z = patch[k2 * kPatchStride + rr];
+                            if (k3 != 0xffu) v.w = patch[k3 * kPatchStride + rr];
+                            __stcs(reinterpret_cast<uint4*>(dst + toff[rr]), v);
+                        }
+                    }
+                }
+            } else {
+                for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                    uint32_t* dst = out + toff[rr] + w0;
+#pragma unroll
+                    for (int c = 0; c < kTileWords / 32; ++c) {
+                        const uint32_t wl = c * 32 + lane;
+                        const uint32_t k = sm.pidx[wl];
+                        if (w0 + wl < words_out && k != 0xffu) {
+                            uint32_t v;
+                            if (dense) {
+                                const uint32_t thr = rr + 1;
+                                v = ~0u;
+#pragma unroll
+                                for (int q = 0; q < 7; ++q) {
+                                    const uint32_t pl = sm.cntp[q * kTileWords + wl];
+                                    v = ((thr >> q) & 1u) ? (v & pl) : (v | pl);
+                                }
+                            } else {
+                                v = patch[k * kPatchStride + rr];
+                            }
+                            __stcs(dst + wl, v);
+                        }
+                    }
+                }
+            }
+        }
+        if (tid == 0) {  // everyone copied these to registers right after phase A
+            GS_TRACE(6);
+            sm.n_partial = 0;
+            sm.n_heavy = 0;
+        }
+        __syncthreads();  // phase A of the next tile rewrites what this tile was reading
+        GS_TRACE(7);
+        cur = sm.next_tile;
+    }
+    GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 2);
+    // the last CTA out re-arms the ticket counter for the next launch and publishes this one
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(&fb.sched[1], 1u) == gridDim.x - 1) {
+            fb.sched[0] = 0;
+            fb.sched[1] = 0;
+            __threadfence();
+            atomicAdd(fb.expand_epoch, 1u);
+            // completion stays transitive along the stream even when this grid did not wait at its start
+            // (one lingering thread holds the grid open)
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+        }
+    }
+}
 
 // ------------------------------------------------------------------------------------------------
 // launchers
@@ -440,6 +909,11 @@ static cudaError_t ensure_attrs(int device) {
     if (device >= 0 && device < 64 && g_attr_done[device]) return cudaSuccess;
     cudaError_t e = cudaFuncSetAttribute(k_radix_sort<BindKeyLoader>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)kSortSmemBytes);
+    if (e != cudaSuccess) return e;
+    // k_expand wants as many resident CTAs as its shared memory allows: ask for the largest carve-out
+    e = cudaFuncSetAttribute(k_expand<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_expand<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
     if (device >= 0 && device < 64) g_attr_done[device] = true;
     return cudaSuccess;
@@ -479,93 +953,62 @@ cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do
                               dev_stride, n_words, ov, expand_epoch_wanted);
 }
 
-// Shape of the tile grid for one launch; k_settle and k_expand must agree on it.
-struct TileGeometry {
-    bool vec;
-    uint32_t words_out, n_col_blocks, n_row_tiles, n_tiles, inv_col_blocks;
-};
-static TileGeometry tile_geometry(uint32_t n_pods, uint32_t words, uint32_t row_stride, const uint32_t* d_out) {
-    TileGeometry g;
-    g.vec = (row_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_out) & 15u) == 0);
+cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
+                          uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted,
+                          cudaStream_t st) {
+    if (n_pods == 0 || words == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaError_t ea = ensure_attrs(dev);
+        if (ea != cudaSuccess) return ea;
+    }
+    const bool vec = (row_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_out) & 15u) == 0);
     // 16-byte stores; the row's last 32-byte sector is written whole when the stride leaves room for it (a
     // half-written sector costs a read-modify-write in DRAM: profiles/NOTES.md).  Padding bits are zero.
-    g.words_out = words;
-    if (g.vec) {
-        g.words_out = (words + 7u) & ~7u;
-        if (g.words_out > row_stride) g.words_out = (words + 3u) & ~3u;
+    uint32_t words_out = words;
+    if (vec) {
+        words_out = (words + 7u) & ~7u;
+        if (words_out > row_stride) words_out = (words + 3u) & ~3u;
     }
-    g.n_col_blocks = (g.words_out + kTileWords - 1) / kTileWords;
-    g.n_row_tiles = (n_pods + kTileRows - 1) / kTileRows;
-    g.n_tiles = g.n_col_blocks * g.n_row_tiles;
+    const uint32_t n_col_blocks = (words_out + kTileWords - 1) / kTileWords;
+    const uint32_t n_row_tiles = (n_pods + kTileRows - 1) / kTileRows;
+    const uint32_t n_tiles = n_col_blocks * n_row_tiles;
+    // Four CTAs per SM stream as fast as five (tools/chunk_write_bw.cu), and the fifth slot's registers and
+    // threads are what lets every block of the next batch's k_prep become resident next to a running k_expand
+    // (a programmatic dependent is launched only when ALL blocks of its primary have started).  The limit is
+    // set through shared memory: static (36 KB) + this unused dynamic pad + 1 KB reserved > 228 KB / 5.
+    const uint32_t per_sm = 4;
+    constexpr uint32_t kOccupancyPadBytes = 10240;
+    uint32_t grid = (uint32_t)sm_count * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+
     // exact t / n_col_blocks as a multiply-high for every t below 2^32 / n_col_blocks (n_tiles is far
     // smaller); 0 stands for "one column block" (2^32 does not fit)
-    g.inv_col_blocks = g.n_col_blocks == 1 ? 0u : (uint32_t)((0x100000000ull + g.n_col_blocks - 1) / g.n_col_blocks);
-    return g;
-}
-
-size_t tile_record_bytes() { return sizeof(TileRecord); }
-size_t tile_payload_bytes() { return sizeof(TilePayload); }
-
-static void pdl_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, uint32_t grid, uint32_t block, cudaStream_t st) {
-    cfg = {};
+    const uint32_t inv = n_col_blocks == 1 ? 0u : (uint32_t)((0x100000000ull + n_col_blocks - 1) / n_col_blocks);
+    cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(block);
-    cfg.dynamicSmemBytes = 0;
+    cfg.blockDim = dim3(kExpandThreads);
+    cfg.dynamicSmemBytes = kOccupancyPadBytes;
     cfg.stream = st;
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // may start under the predecessor's tail
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // overlap the launch with k_prep's tail
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-}
-
-cudaError_t launch_settle(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words, uint32_t row_stride,
-                          const uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted, cudaStream_t st) {
-    if (n_pods == 0 || words == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
-    const TileGeometry g = tile_geometry(n_pods, words, row_stride, d_out);
-    // about four CTAs per SM; each takes every n_splits-th row tile of one column block
-    const uint32_t want = (uint32_t)sm_count * 4u;
-    uint32_t splits = want / g.n_col_blocks;
-    const uint32_t min_splits = (g.n_row_tiles + kSettleRowTiles - 1) / kSettleRowTiles;
-    if (splits < min_splits) splits = min_splits;
-    if (splits > g.n_row_tiles) splits = g.n_row_tiles;
-    cudaLaunchConfig_t cfg;
-    cudaLaunchAttribute attr[1];
-    pdl_config(cfg, attr, g.n_col_blocks * splits, kSettleThreads, st);
-    return cudaLaunchKernelEx(&cfg, k_settle, fb, n_pods, g.n_col_blocks, g.n_row_tiles, splits,
-                              overlap_previous ? 1u : 0u, prep_epoch_wanted);
-}
-
-cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
-                          uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t settle_epoch_wanted,
-                          cudaStream_t st) {
-    if (n_pods == 0 || words == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
-    const TileGeometry g = tile_geometry(n_pods, words, row_stride, d_out);
-    // Four CTAs per SM stream as fast as five (tools/chunk_write_bw.cu) and leave registers and threads for
-    // the small kernels of the next batch, all of whose blocks must be resident next to a running k_expand
-    // (a programmatic dependent is launched only when ALL blocks of its primary have started).
-    // The limit holds across overlapping launches because it is set through shared memory: static (6 KB) + this
-    // unused dynamic pad + 1 KB reserved > 228 KB / 5, which still leaves ~40 KB per SM for k_prep and k_settle.
-    const uint32_t per_sm = 4;
-    constexpr uint32_t kOccupancyPadBytes = 40 * 1024;
-    uint32_t grid = (uint32_t)sm_count * per_sm;
-    if (grid > g.n_tiles) grid = g.n_tiles;
-    cudaLaunchConfig_t cfg;
-    cudaLaunchAttribute attr[1];
-    pdl_config(cfg, attr, grid, kExpandThreads, st);
-    cfg.dynamicSmemBytes = kOccupancyPadBytes;
     const uint32_t ov = overlap_previous ? 1u : 0u;
-    if (g.vec)
-        return cudaLaunchKernelEx(&cfg, k_expand<true>, fb, n_pods, g.words_out, row_stride, d_out, g.n_col_blocks,
-                                  g.inv_col_blocks, g.n_tiles, ov, settle_epoch_wanted);
-    return cudaLaunchKernelEx(&cfg, k_expand<false>, fb, n_pods, g.words_out, row_stride, d_out, g.n_col_blocks,
-                              g.inv_col_blocks, g.n_tiles, ov, settle_epoch_wanted);
+    if (vec)
+        return cudaLaunchKernelEx(&cfg, k_expand<true>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles, ov,
+                                  prep_epoch_wanted);
+    return cudaLaunchKernelEx(&cfg, k_expand<false>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles, ov,
+                              prep_epoch_wanted);
 }
 
 }  // namespace gs
 
 #ifdef GS_EXPAND_TRACE
 extern "C" int gs_debug_ktrace_reset() {
-    static unsigned long long lo[64 * 3 * 6], hi[64 * 3 * 6];
+    static unsigned long long lo[64 * 2 * 6], hi[64 * 2 * 6];
     for (auto& v : lo) v = ~0ull;
     for (auto& v : hi) v = 0;
     cudaError_t e = cudaMemcpyToSymbol(gs::g_kmin, lo, sizeof lo);
@@ -576,5 +1019,9 @@ extern "C" int gs_debug_ktrace_read(unsigned long long* lo, unsigned long long* 
     cudaError_t e = cudaMemcpyFromSymbol(lo, gs::g_kmin, sizeof(gs::g_kmin));
     if (e == cudaSuccess) e = cudaMemcpyFromSymbol(hi, gs::g_kmax, sizeof(gs::g_kmax));
     return (int)e;
+}
+extern "C" int gs_debug_expand_trace(unsigned long long* host, size_t n) {
+    if (n > sizeof(gs::g_trace) / 8) n = sizeof(gs::g_trace) / 8;
+    return (int)cudaMemcpyFromSymbol(host, gs::g_trace, n * 8);
 }
 #endif

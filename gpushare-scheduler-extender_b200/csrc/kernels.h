@@ -11,8 +11,6 @@ namespace gs {
 void set_last_error(const char* msg);
 
 // K3 (filter_kernels.cu)
-struct TileRecord;
-struct TilePayload;
 struct FilterBuffers {              // work buffers of one filter launch sequence (HBM scratch)
     unsigned long long* grouped_req;  // [GS_MAX_BATCH] requests in bucket order
     uint16_t* perm;                   // [GS_MAX_BATCH] grouped position -> pod index
@@ -25,10 +23,6 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     uint32_t* prep_done;              // [1] finished blocks of the running k_prep (self re-arming)
     uint32_t* prep_epoch;             // [1] completed k_prep launches on this buffer set
     uint32_t* expand_epoch;           // [1] completed k_expand launches on this buffer set
-    uint32_t* settle_done;            // [1] finished CTAs of the running k_settle (self re-arming)
-    uint32_t* settle_epoch;           // [1] completed k_settle launches on this buffer set
-    TileRecord* records;       // [row tiles x column blocks] per-tile base words (tile_kernels.inc)
-    TilePayload* payloads;     // [row tiles x column blocks] per-row values of the partial words
     uint32_t set_index;               // 0 / 1: which of the two buffer sets this is (development traces)
 };
 cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n, unsigned long long* d_sorted,
@@ -37,13 +31,9 @@ cudaError_t launch_prep(const unsigned long long* d_req, uint32_t n_pods, bool d
                         const FilterBuffers& fb, const unsigned long long* d_used, const unsigned long long* d_cap,
                         const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words,
                         bool overlap_previous, uint32_t expand_epoch_wanted, cudaStream_t st);
-cudaError_t launch_settle(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words, uint32_t row_stride,
-                          const uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted, cudaStream_t st);
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
-                          uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t settle_epoch_wanted,
+                          uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted,
                           cudaStream_t st);
-size_t tile_record_bytes();
-size_t tile_payload_bytes();
 
 // K1 / K2 / K4 (state_kernels.cu)
 cudaError_t launch_validate_records(gs_pod_record* d_pods, uint32_t first, uint32_t n, const uint32_t* d_nodeinfo,

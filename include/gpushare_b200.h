@@ -126,8 +126,7 @@ enum {
     GS_K_EXPAND = 4,
     GS_K_BIND_SORT = 5,
     GS_K_BIND_SCAN = 6,
-    GS_K_SETTLE = 7,
-    GS_K_COUNT_ = 8
+    GS_K_COUNT_ = 7
 };
 
 const char* gs_last_error(void);
@@ -178,8 +177,6 @@ int gs_filter_batch_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pod
 #define GS_STAGE_SORT 1u
 #define GS_STAGE_NODE_RANK 2u
 #define GS_STAGE_EXPAND 4u
-#define GS_STAGE_SETTLE 8u /* runs between NODE_RANK and EXPAND */
-#define GS_STAGE_ALL 15u
 int gs_filter_stages_device(gs_snapshot* s, uint32_t stage_mask, const uint64_t* d_req, uint32_t n_pods,
                             uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream);
 /* Per-node class bytes (GS_NODE_*) for rendering FailedNodes. */

@@ -28,7 +28,7 @@ if os.environ.get("EXPAND_ONLY"):
     call = lambda i: snap.filter_stages_device(4, rp, P, ptrs[i % 4], stride, sh)
 else:
     call = lambda i: snap.filter_batch_device(rp, P, ptrs[i % 4], stride, sh)
-for steps in (200, 1000):
+for steps in [int(x) for x in os.environ.get("STEPS", "200,1000").split(",")]:
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter(); e0.record()
     for i in range(steps): call(i)

@@ -52,9 +52,9 @@ def main():
             continue
         d_req = torch.from_numpy(np.asarray(reqs, dtype=np.int64)).to(dev)
         res = {}
-        for label, mask in (("pods", 1), ("nodes", 2), ("settle", 8), ("expand", 4), ("all", 15)):
+        for label, mask in (("pods", 1), ("nodes", 2), ("expand", 4), ("all", 7)):
             for i in range(3):
-                snap.filter_stages_device(15 if i == 0 else mask, d_req.data_ptr(), P, outs[i % 4].data_ptr(), stride, st.cuda_stream)
+                snap.filter_stages_device(7 if i == 0 else mask, d_req.data_ptr(), P, outs[i % 4].data_ptr(), stride, st.cuda_stream)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
