@@ -436,7 +436,8 @@ def run_product(args):
             "config": {"workload": WORKLOAD, "nodes_per_gpu": N, "devices_per_node": sc.max_devs, "running_pods_per_gpu": sc.n_pods,
                        "pending_pods": P, "requests": REQ_KIND, "bitmap_row_stride_words": stride,
                        "l2": f"{N_OUT_BUFFERS} rotating output buffers of {P * stride * 4 / 1e6:.1f} MB (> 126 MB L2 in total)",
-                       "pipelining": "GS_OPT_PIPELINE_FILTERS: the prep kernel of step k+1 may run under the tail of step k's expand kernel",
+                       "pipelining": "GS_OPT_PIPELINE_FILTERS: consecutive steps overlap on the GPU (prep of step k+1 beside expand of step k, "
+                                     "expand of step k+1 fills the SM slots step k frees); every step runs all of its kernels",
                        "parallelism": f"nodes sharded over {world} GPU(s), weak scaling, no data-path collective"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(gpu_launches),
             "kernel_ms": kernel_ms, "clocks": clocks,

@@ -201,11 +201,15 @@ int gs_host_alloc(size_t bytes, void** out);
 int gs_host_free(void* p);
 
 /* Options.  GS_OPT_PIPELINE_FILTERS (default 0): consecutive gs_filter_batch_device calls on one stream may
- * overlap on the GPU -- the second call's preparation kernel runs under the tail of the first call's bitmap
- * kernel (they use separate work buffers).  Contract when set: the request array of a call must already be
- * complete when the PREVIOUS filter call was enqueued (do not produce it with a kernel enqueued in between; a
- * cudaMemcpyAsync in between is fine, it restores plain stream order), and a call whose output overlaps the
- * previous call's output is not overlapped.  Results are identical either way. */
+ * overlap on the GPU.  The calls rotate through separate work buffers; the second call's preparation kernel
+ * runs beside the first call's bitmap kernel, and its bitmap kernel takes over the SM slots the first one frees
+ * instead of waiting for it to drain (the kernels wait for each other through counters in device memory, not
+ * through stream order).  Contract when set: the request array of a call must already be complete when the
+ * PREVIOUS filter call was enqueued (do not produce it with a kernel enqueued in between; a cudaMemcpyAsync in
+ * between is fine, it restores plain stream order), and a call whose output overlaps the previous call's output
+ * is not overlapped.  Every other entry point ends a chain of overlapping filters.  Results are identical either
+ * way; what the stream guarantees after a call (the bitmap is complete when the stream reaches that point) does
+ * not change.  No counterpart in the reference. */
 enum { GS_OPT_PIPELINE_FILTERS = 1 };
 int gs_set_option(gs_snapshot* s, int option, int value);
 
