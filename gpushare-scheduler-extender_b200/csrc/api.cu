@@ -157,7 +157,7 @@ int filter_chunk(gs_snapshot* s, const u64* d_req, uint32_t n_pods, uint32_t* d_
     fb.grouped_req = s->d_sorted_keys + (size_t)set * GS_MAX_BATCH;
     fb.perm = s->d_perm + (size_t)set * GS_MAX_BATCH;
     fb.row_bucket = s->d_row_bucket + (size_t)set * GS_MAX_BATCH;
-    fb.pod_hist = s->d_pod_hist;
+    fb.pod_hist = s->d_pod_hist + set * 512;
     fb.planes = s->d_rank_planes + (size_t)set * s->rank_words * gs::kRankPlanes;
     fb.node_key = s->d_node_key + (size_t)set * s->rank_words * 32;
     fb.node_key32 = s->d_node_key32 + (size_t)set * s->rank_words * 32;
@@ -277,8 +277,8 @@ int gs_snapshot_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32
     CU_NEW(cudaMalloc(&s->d_node_key, 2 * (size_t)s->rank_words * 32 * sizeof(u64)));
     CU_NEW(cudaMalloc(&s->d_node_key32, 2 * (size_t)s->rank_words * 32 * sizeof(uint32_t)));
     CU_NEW(cudaMalloc(&s->d_row_bucket, 2 * (size_t)GS_MAX_BATCH * sizeof(uint16_t)));
-    CU_NEW(cudaMalloc(&s->d_pod_hist, 516 * sizeof(uint32_t)));
-    CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 516 * sizeof(uint32_t), s->stream));
+    CU_NEW(cudaMalloc(&s->d_pod_hist, 2 * 512 * sizeof(uint32_t)));
+    CU_NEW(cudaMemsetAsync(s->d_pod_hist, 0, 2 * 512 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMalloc(&s->d_epochs, 6 * sizeof(uint32_t)));
     CU_NEW(cudaMemsetAsync(s->d_epochs, 0, 6 * sizeof(uint32_t), s->stream));
     CU_NEW(cudaMalloc(&s->d_sched, 4 * sizeof(uint32_t)));

@@ -50,7 +50,7 @@ struct gs_snapshot {
     unsigned long long* d_sorted_keys = nullptr;  // [GS_MAX_BATCH] (K3/K4 sort output)
     uint16_t* d_perm = nullptr;               // [GS_MAX_BATCH] sorted position -> input index
     uint16_t* d_row_bucket = nullptr;         // [GS_MAX_BATCH] (K3)
-    uint32_t* d_pod_hist = nullptr;           // [516] (K3, self re-arming)
+    uint32_t* d_pod_hist = nullptr;           // [2 sets][512] bucket counts (K3, self re-arming)
     unsigned long long max_capacity = 0;      // largest dev_capacity of an OK node ever upserted (bucket scale)
     uint32_t* d_rank_planes = nullptr;        // [rank_words / kTileWords][kRankPlanes][kTileWords] (K3)
     unsigned long long* d_node_key = nullptr; // [rank_words * 32] (K3)

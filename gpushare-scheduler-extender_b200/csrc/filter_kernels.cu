@@ -328,7 +328,10 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
     }
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     auto may_write = [&]() {
-        if (tid == 0 && (int32_t)(epoch_seen - expand_epoch_wanted) < 0) wait_epoch(fb.expand_epoch, expand_epoch_wanted);
+        if (tid == 0 && (int32_t)(epoch_seen - expand_epoch_wanted) < 0) {
+            wait_epoch(fb.expand_epoch, expand_epoch_wanted);
+            epoch_seen = expand_epoch_wanted;
+        }
         __syncthreads();
         GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 1);
     };
@@ -342,14 +345,20 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         const uint32_t i = blockIdx.x * kPrepThreads + tid;
         uint32_t sl = 0;
         u64 r = 0;
+        if (i < n_pods) r = req[i];
+        // With overlapping batches the k_prep of the batch before the previous one may still be polling this
+        // buffer set's bucket counts: nothing of the set is touched before the expand kernel that last read it
+        // (and therefore that k_prep) is known to be over.  The epoch was read together with the request above.
+        if (overlap_previous) may_write();
         if (i < n_pods) {
-            r = req[i];
             const u64 bq = r >> shift;
             const uint32_t b = bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1;
             sl = (b << 16) | atomicAdd(&ghist[b], 1u);  // arrival number inside the bucket
         }
+#ifdef GS_EXPAND_TRACE
         if (sl == 0xffffffffu) return;  // (never true: makes the stamp below wait for the atomic's result)
         GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 3);
+#endif
         // The counts are complete when they add up to the number of pods: every block polls the 512 counts (the
         // pod blocks are the first blocks of a small grid of small blocks: all of them are resident), and the
         // poll that finds them complete already holds the values the scan needs.
@@ -577,14 +586,17 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
     GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 0);
     if (!overlap_previous) {
         asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     } else {
+        // the next batch's k_prep may start as soon as this grid is resident: it shares nothing with this batch's
+        // k_prep, which may still be running (each buffer set has its own bucket counts)
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         if (tid == 0) {
             wait_epoch(fb.prep_epoch, prep_epoch_wanted);
             asm volatile("fence.proxy.async;" ::: "memory");  // the bulk copies below read what k_prep wrote
         }
         __syncthreads();
     }
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     GS_KTRACE(2 * prep_epoch_wanted + fb.set_index, 1, 1);
     if (tid == 0) request(blockIdx.x, 0);
     __syncthreads();

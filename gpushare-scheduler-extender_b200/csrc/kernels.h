@@ -15,7 +15,7 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     unsigned long long* grouped_req;  // [GS_MAX_BATCH] requests in bucket order
     uint16_t* perm;                   // [GS_MAX_BATCH] grouped position -> pod index
     uint16_t* row_bucket;             // [GS_MAX_BATCH] 1-based bucket of every grouped row
-    uint32_t* pod_hist;               // [512 + 2] bucket counts, arrived / finished block counters (self re-arming)
+    uint32_t* pod_hist;               // [512] bucket counts of this buffer set (zero between launches)
     uint32_t* planes;                 // [words / kTileWords][kRankPlanes][kTileWords] node bucket ids, bit-sliced
     unsigned long long* node_key;     // [words * 32] max available memory per node
     uint32_t* node_key32;             // [words * 32] the same, saturated to 32 bits
