@@ -702,16 +702,24 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         }
         // D, first part: lane owns 4 words, warp owns rows warp, warp + kWarps, ...; 16 bytes per lane, 512
         // contiguous bytes per warp and row.  Lanes whose four words are the same in every row store now.
-        const uint32_t wcol = w0 + lane * 4;
+        // In a narrow last column block the lanes of a warp are spread over several rows instead (lanes_per_row
+        // lanes each), so that a store instruction still covers 512 bytes: a warp's worth of 128-byte row ends
+        // costs as much store-pipe time as full rows.
+        const uint32_t width4 = min(32u, (words_out - w0) >> 2);  // 16-byte columns of this tile (kVec)
+        const uint32_t lane_shift = width4 > 16 ? 5u : width4 > 8 ? 4u : width4 > 4 ? 3u : width4 > 2 ? 2u : width4 > 1 ? 1u : 0u;
+        const uint32_t lcol = lane & ((1u << lane_shift) - 1u);      // the lane's 16-byte column
+        const uint32_t row0 = (warp << (5u - lane_shift)) + (lane >> lane_shift);  // its first row
+        const uint32_t row_step = kWarps << (5u - lane_shift);
+        const uint32_t wcol = w0 + lcol * 4;
         uint4 b4 = make_uint4(0, 0, 0, 0);
         uint32_t p4 = 0xffffffffu;
         if (kVec) {
-            b4 = *reinterpret_cast<const uint4*>(&sm.basew[lane * 4]);
-            p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lane * 4]);
+            b4 = *reinterpret_cast<const uint4*>(&sm.basew[lcol * 4]);
+            p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lcol * 4]);
             if (wcol < words_out && p4 == 0xffffffffu) {
                 uint32_t* dst = out + wcol;
 #pragma unroll 4
-                for (uint32_t rr = warp; rr < rows; rr += kWarps)
+                for (uint32_t rr = row0; rr < rows; rr += row_step)
                     __stcs(reinterpret_cast<uint4*>(dst + sm.row_off[rr]), b4);
             }
         } else {
@@ -830,13 +838,13 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     uint32_t* dst = out + wcol;
                     const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
                     if (dense) {
-                        for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                        for (uint32_t rr = row0; rr < rows; rr += row_step) {
                             // bit set iff the node's pass count reaches (sorted) row + 1
                             const uint32_t thr = rr + 1;
                             uint4 ge = make_uint4(~0u, ~0u, ~0u, ~0u);
 #pragma unroll
                             for (int q = 0; q < 7; ++q) {
-                                const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lane * 4]);
+                                const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lcol * 4]);
                                 if ((thr >> q) & 1u) {
                                     ge.x &= pl.x; ge.y &= pl.y; ge.z &= pl.z; ge.w &= pl.w;
                                 } else {
@@ -851,7 +859,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             __stcs(reinterpret_cast<uint4*>(dst + toff[rr]), v);
                         }
                     } else {
-                        for (uint32_t rr = warp; rr < rows; rr += kWarps) {
+                        for (uint32_t rr = row0; rr < rows; rr += row_step) {
                             uint4 v = b4;
                             if (k0 != 0xffu) v.x = patch[k0 * kPatchStride + rr];
                             if (k1 != 0xffu) v.y = patch[k1 * kPatchStride + rr];
