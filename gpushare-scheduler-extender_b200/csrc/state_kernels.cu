@@ -64,13 +64,20 @@ k_rebuild(const gs_pod_record* __restrict__ pods, uint32_t n_slots, uint32_t dev
     __syncthreads();
     const uint32_t base = win_base;
 
+    // all of the thread's records first (independent 16-byte loads in flight together), the arithmetic after
+    gs_pod_record recs[kRebuildItems];
 #pragma unroll
     for (int it = 0; it < kRebuildItems; ++it) {
         const uint32_t i = cta_first + it * kRebuildThreads + tid;
+        recs[it].flags = 0;
+        if (i < n_slots) recs[it] = load_record(pods + i);
+    }
+#pragma unroll
+    for (int it = 0; it < kRebuildItems; ++it) {
         uint32_t bin = 0xffffffffu;
         u64 val = 0;
-        if (i < n_slots) {
-            gs_pod_record r = load_record(pods + i);
+        {
+            const gs_pod_record r = recs[it];
             if ((r.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED)) {
                 bin = r.node_idx * dev_stride + (uint32_t)r.dev;
                 val = r.mem;

@@ -243,3 +243,44 @@ def test_pipelined_mixed_sizes_and_state_changes():
             after = S.pack_bitmap(S.filter_pass(batches[i], key1, elig1), stride)
             assert (first[i] == (before if i < 6 else after)).all(), ("first pass", i)
             assert (last[i] == after).all(), ("last pass", i)
+
+
+def test_pipelined_c4_hard_request_distributions():
+    """Full-size config C4 with the request distributions that stress the tile classification: every row inside
+    the crowded key buckets (all tiles dense), every row above the largest capacity (open-ended last bucket),
+    requests that do not fit 32 bits (wrapped negative sums: the 64-bit key path), zeros, and a mix.  Ten thousand
+    pods each, enqueued back to back with pipelining on; bit-exact against the flat-array restatement."""
+    import torch
+
+    sc = synth.make_config("C4")
+    cap, used, ndev, cls, _ = H.soa_state(sc)
+    key, elig = S.node_keys(cap, used, ndev, cls)
+    P = 10000
+    rng = np.random.default_rng(11)
+    wide = rng.integers(1, 184320, P).astype(np.uint64)
+    wide[::7] = np.uint64(2**64 - 1) - rng.integers(0, 5000, len(wide[::7])).astype(np.uint64)  # uint(negative sum)
+    wide[3::11] = np.uint64(2**40) + rng.integers(0, 99, len(wide[3::11])).astype(np.uint64)
+    mix = np.concatenate([rng.integers(180000, 184321, P // 2), rng.integers(0, 3, P // 4), rng.integers(150000, 400000, P - P // 2 - P // 4)]).astype(np.uint64)
+    rng.shuffle(mix)
+    batches = [
+        rng.integers(180000, 184321, P).astype(np.uint64),   # all rows in the crowded buckets
+        np.full(P, 1_000_000, dtype=np.uint64),               # open-ended bucket only
+        wide,
+        np.zeros(P, dtype=np.uint64),
+        mix,
+    ]
+    with H.load_snapshot(sc) as s:
+        s.set_option(gsx.capi.OPT_PIPELINE_FILTERS, 1)
+        stride = (s.bitmap_words + 7) // 8 * 8
+        st = torch.cuda.Stream()
+        d_reqs = [torch.from_numpy(b.view(np.int64)).cuda() for b in batches]
+        outs = [torch.full((P, stride), -1, dtype=torch.int32, device="cuda") for _ in batches]
+        torch.cuda.synchronize()
+        for rep in range(2):
+            for d_req, o in zip(d_reqs, outs):
+                s.filter_batch_device(d_req.data_ptr(), P, o.data_ptr(), stride, st.cuda_stream)
+        st.synchronize()
+        for i, (b, o) in enumerate(zip(batches, outs)):
+            got = o.cpu().numpy().view(np.uint32)
+            want = S.pack_bitmap(S.filter_pass(b, key, elig), stride)
+            assert (got == want).all(), i
