@@ -350,10 +350,17 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         // buffer set's bucket counts: nothing of the set is touched before the expand kernel that last read it
         // (and therefore that k_prep) is known to be over.  The epoch was read together with the request above.
         if (overlap_previous) may_write();
-        if (i < n_pods) {
+        {
+            // arrival number inside the bucket: the lanes of a warp that share a bucket go to L2 as one atomic
+            // (real request mixes have a handful of popular sizes: one address would take 10 000 atomics in turn)
             const u64 bq = r >> shift;
-            const uint32_t b = bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1;
-            sl = (b << 16) | atomicAdd(&ghist[b], 1u);  // arrival number inside the bucket
+            const uint32_t b = i < n_pods ? (bq < kBuckets - 1 ? (uint32_t)bq : kBuckets - 1) : kBuckets + lane;
+            const uint32_t same = __match_any_sync(0xffffffffu, b);
+            const uint32_t leader = __ffs(same) - 1;
+            uint32_t first = 0;
+            if (lane == leader && i < n_pods) first = atomicAdd(&ghist[b], (uint32_t)__popc(same));
+            first = __shfl_sync(0xffffffffu, first, leader);
+            if (i < n_pods) sl = (b << 16) | (first + __popc(same & ((1u << lane) - 1u)));
         }
 #ifdef GS_EXPAND_TRACE
         if (sl == 0xffffffffu) return;  // (never true: makes the stamp below wait for the atomic's result)
