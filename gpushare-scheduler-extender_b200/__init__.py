@@ -7,6 +7,6 @@ The directory name carries a hyphen, so import it with
 from . import build  # noqa: F401
 from . import capi  # noqa: F401
 from . import ext  # noqa: F401
-from .capi import GpushareError, PinnedBuffer, Snapshot, unpack_bitmap  # noqa: F401
+from .capi import GpushareError, PinnedBuffer, Snapshot, expand_compact, unpack_bitmap  # noqa: F401
 
-__all__ = ["build", "capi", "GpushareError", "PinnedBuffer", "Snapshot", "unpack_bitmap"]
+__all__ = ["build", "capi", "GpushareError", "PinnedBuffer", "Snapshot", "expand_compact", "unpack_bitmap"]

@@ -11,8 +11,8 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libgpushare_b200.so")
 
-SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu", "noalloc.cu", "ext.cpp"]
-HEADERS = ["common.cuh", "kernels.h", "exports.map", "ext_state.inc", "ext_handlers.inc",
+SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu", "compact_kernels.cu", "noalloc.cu", "ext.cpp"]
+HEADERS = ["common.cuh", "kernels.h", "state_device.cuh", "exports.map", "ext_state.inc", "ext_handlers.inc",
            os.path.join(ROOT, "include", "gpushare_ext.h"), os.path.join(ROOT, "include", "gpushare_b200.h")]
 
 NVCC_FLAGS = [

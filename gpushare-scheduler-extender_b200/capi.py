@@ -16,12 +16,12 @@ GS_OK, GS_ERR_INVALID, GS_ERR_CUDA, GS_ERR_CAPACITY, GS_ERR_NOMEM = 0, -1, -2, -
 NODE_OK, NODE_NOT_FOUND, NODE_NOT_SHARE = 0, 1, 2
 EV_ADD, EV_REMOVE = 0, 1
 POD_VALID, POD_COUNTED = 1, 2
-BIND_NO_DEVICE, BIND_NODE_NOT_FOUND = -1, -2
+BIND_NO_DEVICE, BIND_NODE_NOT_FOUND, BIND_SLOT_BUSY = -1, -2, -3
 MAX_DEVS, MAX_BATCH = 64, 12288
 STAGE_SORT, STAGE_NODE_RANK, STAGE_EXPAND = 1, 2, 4
 OPT_PIPELINE_FILTERS = 1
-K_REBUILD, K_APPLY, K_SORT, K_NODE_RANK, K_EXPAND, K_BIND_SORT, K_BIND_SCAN = range(7)
-KERNEL_NAMES = ["rebuild", "apply", "sort", "node_rank", "expand", "bind_sort", "bind_scan"]
+K_REBUILD, K_APPLY, K_SORT, K_NODE_RANK, K_EXPAND, K_BIND_SORT, K_BIND_SCAN, K_COMPACT, K_SUBSET = range(9)
+KERNEL_NAMES = ["rebuild", "apply", "sort", "node_rank", "expand", "bind_sort", "bind_scan", "compact", "subset"]
 
 # numpy mirrors of the C structs (layouts asserted against sizeof in tests/test_abi.py)
 NODE_DT = np.dtype([("dev_capacity", "<u8"), ("node_idx", "<u4"), ("dev_count", "<u4"),
@@ -39,6 +39,8 @@ EXPORTS = [
     "gs_filter_batch_device", "gs_filter_stages_device", "gs_node_classes", "gs_bind_batch", "gs_bind_rollback", "gs_inspect",
     "gs_read_used", "gs_read_pods", "gs_host_alloc", "gs_host_free", "gs_profile_enable", "gs_profile_read",
     "gs_profile_reset", "gs_launch_count", "gs_device_ptrs", "gs_pods_apply_static", "gs_set_option",
+    "gs_pods_apply_async", "gs_snapshot_sync", "gs_snapshot_external_write", "gs_filter_batch_subset",
+    "gs_filter_batch_compact", "gs_filter_batch_compact_device", "gs_sm_count",
 ]
 
 
@@ -96,6 +98,13 @@ def load():
         "gs_device_ptrs": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
         "gs_pods_apply_static": (C.c_int, [C.c_int, vp, u32, vp, u32, vp, u32, u32, vp, vp]),
         "gs_set_option": (C.c_int, [vp, C.c_int, C.c_int]),
+        "gs_pods_apply_async": (C.c_int, [vp, vp, u32]),
+        "gs_snapshot_sync": (C.c_int, [vp]),
+        "gs_snapshot_external_write": (C.c_int, [vp, vp]),
+        "gs_filter_batch_subset": (C.c_int, [vp, vp, u32, vp, u32, vp, u32]),
+        "gs_filter_batch_compact": (C.c_int, [vp, vp, u32, vp, u32, vp]),
+        "gs_filter_batch_compact_device": (C.c_int, [vp, vp, u32, vp, u32, vp, vp]),
+        "gs_sm_count": (C.c_int, [vp, C.POINTER(C.c_int)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -207,6 +216,17 @@ class Snapshot:
         events = np.ascontiguousarray(events, dtype=EVENT_DT)
         _check(load().gs_pods_apply(self.h, _ptr(events), len(events)))
 
+    def pods_apply_async(self, events: np.ndarray):
+        """Queued on the GPU when this returns; every later call of the snapshot sees the batch applied."""
+        events = np.ascontiguousarray(events, dtype=EVENT_DT)
+        _check(load().gs_pods_apply_async(self.h, _ptr(events), len(events)))
+
+    def sync(self):
+        _check(load().gs_snapshot_sync(self.h))
+
+    def external_write(self, stream: int = 0):
+        _check(load().gs_snapshot_external_write(self.h, C.c_void_p(stream)))
+
     # ---- filter ----
     def filter_batch(self, req, row_stride_words: int | None = None, out: np.ndarray | None = None) -> np.ndarray:
         req = np.ascontiguousarray(req, dtype=np.uint64)
@@ -216,6 +236,35 @@ class Snapshot:
         assert out.dtype == np.uint32 and out.flags.c_contiguous and out.shape == (len(req), stride)
         _check(load().gs_filter_batch(self.h, _ptr(req), len(req), _ptr(out), stride))
         return out
+
+    def filter_batch_subset(self, req, node_subset, row_stride_words: int | None = None) -> np.ndarray:
+        """[P][stride] words over the candidate list: bit c of row p = predicate(pod p, node node_subset[c])."""
+        req = np.ascontiguousarray(req, dtype=np.uint64)
+        sub = np.ascontiguousarray(node_subset, dtype=np.uint32)
+        stride = row_stride_words if row_stride_words is not None else max(1, (len(sub) + 31) // 32)
+        out = np.empty((len(req), stride), dtype=np.uint32)
+        _check(load().gs_filter_batch_subset(self.h, _ptr(req), len(req), _ptr(sub), len(sub), _ptr(out), stride))
+        return out
+
+    def filter_batch_compact(self, req, rank_stride: int | None = None, out_rank: np.ndarray | None = None,
+                             out_cutoff: np.ndarray | None = None):
+        """(rank[chunks][stride] u16, cutoff[P] u16): pass(p, n) <=> rank[p // MAX_BATCH, n] >= cutoff[p]."""
+        req = np.ascontiguousarray(req, dtype=np.uint64)
+        stride = rank_stride if rank_stride is not None else self.node_count
+        chunks = max(1, (len(req) + MAX_BATCH - 1) // MAX_BATCH)
+        if out_rank is None:
+            out_rank = np.empty((chunks, stride), dtype=np.uint16)
+        if out_cutoff is None:
+            out_cutoff = np.empty(len(req), dtype=np.uint16)
+        assert out_rank.dtype == np.uint16 and out_rank.flags.c_contiguous and out_rank.shape == (chunks, stride)
+        assert out_cutoff.dtype == np.uint16 and out_cutoff.flags.c_contiguous and len(out_cutoff) == len(req)
+        _check(load().gs_filter_batch_compact(self.h, _ptr(req), len(req), _ptr(out_rank), stride, _ptr(out_cutoff)))
+        return out_rank, out_cutoff
+
+    def filter_batch_compact_device(self, d_req_ptr: int, n_pods: int, d_rank_ptr: int, rank_stride: int, d_cutoff_ptr: int,
+                                    stream: int = 0):
+        _check(load().gs_filter_batch_compact_device(self.h, C.c_void_p(d_req_ptr), n_pods, C.c_void_p(d_rank_ptr),
+                                                     rank_stride, C.c_void_p(d_cutoff_ptr), C.c_void_p(stream)))
 
     def filter_batch_device(self, d_req_ptr: int, n_pods: int, d_out_ptr: int, row_stride_words: int, stream: int = 0):
         _check(load().gs_filter_batch_device(self.h, C.c_void_p(d_req_ptr), n_pods, C.c_void_p(d_out_ptr),
@@ -281,6 +330,12 @@ class Snapshot:
         return dict(used=p[0].value, capacity=p[1].value, nodeinfo=p[2].value, pods=p[3].value)
 
     @property
+    def sm_count(self) -> int:
+        v = C.c_int()
+        _check(load().gs_sm_count(self.h, C.byref(v)))
+        return v.value
+
+    @property
     def launch_count(self) -> int:
         v = C.c_uint64()
         _check(load().gs_launch_count(self.h, C.byref(v)))
@@ -296,6 +351,20 @@ def pods_apply_static(device: int, d_events: int, n_events: int, d_pods: int, n_
     _check(load().gs_pods_apply_static(device, C.c_void_p(d_events), n_events, C.c_void_p(d_pods), n_slots,
                                        C.c_void_p(d_nodeinfo), n_nodes, dev_stride, C.c_void_p(d_used),
                                        C.c_void_p(stream)))
+
+
+def expand_compact(rank: np.ndarray, cutoff: np.ndarray, n_nodes: int, row_stride_words: int | None = None) -> np.ndarray:
+    """What a caller of gs_filter_batch_compact does to get bitmap rows back (plain host arithmetic, here in
+    numpy for tests and bench.py): bit n of row p = rank[p // MAX_BATCH, n] >= cutoff[p]."""
+    words = (n_nodes + 31) // 32
+    stride = row_stride_words if row_stride_words is not None else words
+    out = np.zeros((len(cutoff), stride), dtype=np.uint32)
+    for k in range(rank.shape[0]):
+        lo, hi = k * MAX_BATCH, min(len(cutoff), (k + 1) * MAX_BATCH)
+        bits = np.zeros((hi - lo, words * 32), dtype=np.uint8)
+        bits[:, :n_nodes] = rank[k, :n_nodes][None, :] >= cutoff[lo:hi, None]
+        out[lo:hi, :words] = np.packbits(bits, axis=1, bitorder="little").view(np.uint32).reshape(hi - lo, words)
+    return out
 
 
 def unpack_bitmap(bitmap: np.ndarray, n_nodes: int) -> np.ndarray:

@@ -238,9 +238,48 @@ __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void wait_epoch(const uint32_t* p, uint32_t want) {
-    while ((int32_t)(ld_acquire_u32(p) - want) < 0) {
+
+// Every wait on another kernel's progress is bounded.  The waits below rest on assumptions about the launches
+// around them (the awaited grid is resident or will become resident; counters are zero between launches); if one
+// of them is ever broken -- a launch that was aborted and left its counters behind, a kernel of this library
+// driven from outside the entry points -- the waiter says where it was stuck (a word in mapped host memory that
+// the host reads when the next call fails) and traps, which ends the kernel with an error instead of holding
+// the GPU for ever.
+constexpr unsigned long long kSpinLimitNs = 4000000000ull;  // far above anything a healthy wait can last
+enum : unsigned int {  // what gs_last_error() reports after such a trap
+    kFaultPrepEpoch = 1,    // k_prep waiting for the expand kernel that last read its buffer set
+    kFaultPodCounts = 2,    // k_prep pod blocks waiting for the other pod blocks' bucket counts
+    kFaultExpandEpoch = 3,  // k_expand waiting for its own batch's k_prep
+    kFaultTileInputs = 4,   // k_expand waiting for a bulk copy of tile inputs
+    kFaultTileKeys = 5      // k_expand waiting for a bulk copy of node keys
+};
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __noinline__ void spin_give_up(unsigned int* fault, unsigned int where) {
+    if (fault) {
+        *reinterpret_cast<volatile unsigned int*>(fault) = where;
+        __threadfence_system();
     }
+    __trap();
+}
+struct SpinGuard {
+    unsigned long long t0 = 0;
+    uint32_t n = 0;
+    __device__ __forceinline__ void tick(unsigned int* fault, unsigned int where) {
+        if ((++n & 255u) != 0) return;
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0)
+            t0 = now;
+        else if (now - t0 > kSpinLimitNs)
+            spin_give_up(fault, where);
+    }
+};
+__device__ __forceinline__ void wait_epoch(const uint32_t* p, uint32_t want, unsigned int* fault, unsigned int where) {
+    SpinGuard g;
+    while ((int32_t)(ld_acquire_u32(p) - want) < 0) g.tick(fault, where);
 }
 
 constexpr int kPrepThreads = 128;  // small blocks: they fit next to a fully resident k_expand of the previous batch
@@ -329,7 +368,7 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     auto may_write = [&]() {
         if (tid == 0 && (int32_t)(epoch_seen - expand_epoch_wanted) < 0) {
-            wait_epoch(fb.expand_epoch, expand_epoch_wanted);
+            wait_epoch(fb.expand_epoch, expand_epoch_wanted, fb.fault, kFaultPrepEpoch);
             epoch_seen = expand_epoch_wanted;
         }
         __syncthreads();
@@ -371,6 +410,7 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         // poll that finds them complete already holds the values the scan needs.
         uint4 c4;
         uint32_t run;
+        SpinGuard poll_guard;
         for (;;) {
             c4 = __ldcg(reinterpret_cast<const uint4*>(ghist) + tid);
             const uint32_t sum = c4.x + c4.y + c4.z + c4.w;
@@ -392,6 +432,7 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
             }
             __syncthreads();  // wsum is rewritten by the next poll
             if (total == n_pods) break;
+            poll_guard.tick(fb.fault, kFaultPodCounts);
         }
         GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 4);
         base[tid * 4 + 0] = run;
@@ -507,18 +548,26 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
+    return ok != 0;
+}
+// try_wait suspends the thread for a while by itself; the deadline is only looked at when it keeps failing
+__device__ __noinline__ void mbar_wait_slow(uint64_t* bar, uint32_t parity, unsigned int* fault, unsigned int where) {
+    SpinGuard g;
+    while (!mbar_try_wait(bar, parity)) g.tick(fault, where);
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, unsigned int* fault, unsigned int where) {
+    if (!mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity, fault, where);
 }
 __device__ __forceinline__ void bulk_load(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -599,7 +648,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         // k_prep, which may still be running (each buffer set has its own bucket counts)
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         if (tid == 0) {
-            wait_epoch(fb.prep_epoch, prep_epoch_wanted);
+            wait_epoch(fb.prep_epoch, prep_epoch_wanted, fb.fault, kFaultExpandEpoch);
             asm volatile("fence.proxy.async;" ::: "memory");  // the bulk copies below read what k_prep wrote
         }
         __syncthreads();
@@ -618,7 +667,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         const uint32_t w0 = cb * kTileWords;
         const TileInputs& in = tin[stage];
         GS_TRACE(0);
-        mbar_wait(&tin_bar[stage], parity);
+        mbar_wait(&tin_bar[stage], parity, fb.fault, kFaultTileInputs);
         GS_TRACE(1);
 
         // A: one thread per word (threads 0..127), one per row (threads 128..191)
@@ -753,7 +802,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                         mbar_expect_tx(&key_bar, kStageWords * 4u);
                         bulk_load(stage64, fb.node_key + (size_t)(w0 + 64u) * 32, kStageWords * 4u, &key_bar);
                     }
-                    mbar_wait(&key_bar, key_phase);
+                    mbar_wait(&key_bar, key_phase, fb.fault, kFaultTileKeys);
                     key_phase ^= 1u;
                     GS_TRACE(11);
                     // each warp owns partial words warp, warp + 8, ... and runs four of them at a time, so
@@ -804,7 +853,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                 }
             } else {
                 // C: lane = row; the compared nodes' keys come from the staged 32 keys of the word
-                mbar_wait(&key_bar, key_phase);
+                mbar_wait(&key_bar, key_phase, fb.fault, kFaultTileKeys);
                 key_phase ^= 1u;
                 uint32_t* const patch = sm.stage + kSparseKeyWords;
                 for (uint32_t k = warp; k < np; k += kWarps) {

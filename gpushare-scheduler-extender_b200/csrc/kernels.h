@@ -24,6 +24,7 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     uint32_t* prep_epoch;             // [1] completed k_prep launches on this buffer set
     uint32_t* expand_epoch;           // [1] completed k_expand launches on this buffer set
     uint32_t set_index;               // 0 / 1: which of the two buffer sets this is (development traces)
+    unsigned int* fault;              // mapped host word: where a kernel gave up a bounded wait (may be null)
 };
 cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n, unsigned long long* d_sorted,
                               uint16_t* d_perm, cudaStream_t st);
@@ -37,8 +38,9 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
 
 // K1 / K2 / K4 (state_kernels.cu)
 cudaError_t launch_validate_records(gs_pod_record* d_pods, uint32_t first, uint32_t n, const uint32_t* d_nodeinfo,
-                                    uint32_t n_nodes, cudaStream_t st);
-cudaError_t launch_rebuild(const gs_pod_record* d_pods, uint32_t n_slots, uint32_t dev_stride,
+                                    uint32_t n_nodes, uint32_t dev_stride, cudaStream_t st);
+// zeroes used[0 .. n_node_rows * dev_stride) and adds up the table: two launches
+cudaError_t launch_rebuild(const gs_pod_record* d_pods, uint32_t n_slots, uint32_t n_node_rows, uint32_t dev_stride,
                            unsigned long long* d_used, int sm_count, cudaStream_t st);
 cudaError_t launch_apply_events(const gs_pod_event* d_events, uint32_t n, gs_pod_record* d_pods, uint32_t max_pods,
                                 int32_t* d_last_ev, const uint32_t* d_nodeinfo, uint32_t n_nodes,
@@ -48,5 +50,20 @@ cudaError_t launch_bind_scan(const gs_bind_req* d_binds, uint32_t n, const unsig
                              const uint32_t* d_nodeinfo, uint32_t n_nodes, const unsigned long long* d_cap,
                              uint32_t dev_stride, unsigned long long* d_used, int32_t* d_out_dev, cudaStream_t st);
 cudaError_t launch_fill_i32(int32_t* d, int32_t v, size_t n, cudaStream_t st);
+
+// compact and candidate-list forms of K3 (compact_kernels.cu)
+// Splits the pairwise count of n_pods requests into column slices; returns the number of slices used.
+uint32_t compact_splits(uint32_t n_pods, int sm_count);
+// rank[n] = #{p : req[p] <= key[n]} (0 for a node that can never pass), cutoff[p] = 1 + #{q : req[q] < req[p]}:
+// pass(p, n) <=> rank[n] >= cutoff[p].  Three launches; returns how many were made through *n_launches.
+cudaError_t launch_compact(const unsigned long long* d_req, uint32_t n_pods, uint32_t* d_part, unsigned long long* d_sorted,
+                           uint32_t* d_dup, const unsigned long long* d_used, const unsigned long long* d_cap,
+                           const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint16_t* d_rank,
+                           uint16_t* d_cutoff, int sm_count, cudaStream_t st, uint32_t* n_launches);
+// bit c of row p = predicate(pod p, node subset[c]); one launch
+cudaError_t launch_filter_subset(const unsigned long long* d_req, uint32_t n_pods, const uint32_t* d_subset, uint32_t n_cand,
+                                 const unsigned long long* d_used, const unsigned long long* d_cap,
+                                 const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint32_t* d_out,
+                                 uint32_t row_stride, cudaStream_t st);
 
 }  // namespace gs

@@ -13,6 +13,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "state_device.cuh"
 
 namespace {
 
@@ -35,57 +36,25 @@ int static_fail(int code, const char* fmt, ...) {
     return code;
 }
 
-__device__ __forceinline__ bool names_a_device(const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, uint32_t node, int dev) {
-    if (node >= n_nodes || dev < 0) return false;
-    return (uint32_t)dev < gs::nodeinfo_ndev(nodeinfo[node]);
-}
-__device__ __forceinline__ bool takes_effect(const gs_pod_event& e, uint32_t n_slots, const uint32_t* __restrict__ nodeinfo,
-                                             uint32_t n_nodes) {
-    if (e.slot >= n_slots) return false;
-    if (e.op == GS_EV_REMOVE) return true;
-    return names_a_device(nodeinfo, n_nodes, e.node_idx, e.dev);
-}
-
 __global__ void k_static_clear(int32_t* last_event, uint32_t n_slots) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n_slots) last_event[i] = -1;
 }
 
+// The two passes are the ones gs_pods_apply runs (state_device.cuh): what an event means is defined once.
 // pass 1: the last effective event of every slot
 __global__ void k_static_mark(const gs_pod_event* __restrict__ ev, uint32_t n, uint32_t n_slots, int32_t* last_event,
-                              const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const gs_pod_event e = ev[i];
-    if (takes_effect(e, n_slots, nodeinfo, n_nodes)) atomicMax(&last_event[e.slot], (int32_t)i);
+                              const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, uint32_t dev_stride) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) gs::event_mark(i, ev, n_slots, last_event, nodeinfo, n_nodes, dev_stride);
 }
 
-// pass 2: apply exactly those (additions commute mod 2^64, so used[] ends as if applied in order)
+// pass 2: apply exactly those (the scratch is not re-armed here: every call clears what it is about to use)
 __global__ void k_static_apply(const gs_pod_event* __restrict__ ev, uint32_t n, gs_pod_record* pods, uint32_t n_slots,
-                               const int32_t* __restrict__ last_event, const uint32_t* __restrict__ nodeinfo,
-                               uint32_t n_nodes, uint32_t dev_stride, unsigned long long* used) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const gs_pod_event e = ev[i];
-    if (!takes_effect(e, n_slots, nodeinfo, n_nodes)) return;
-    if (last_event[e.slot] != (int32_t)i) return;
-    const gs_pod_record old = pods[e.slot];
-    if ((old.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED) && old.mem)
-        atomicAdd(&used[(size_t)old.node_idx * dev_stride + (uint32_t)old.dev], 0ull - old.mem);
-    gs_pod_record now;
-    now.mem = 0;
-    now.node_idx = 0;
-    now.dev = 0;
-    now.flags = 0;
-    now.pad_ = 0;
-    if (e.op == GS_EV_ADD) {
-        now.mem = e.mem;
-        now.node_idx = e.node_idx;
-        now.dev = e.dev;
-        now.flags = (uint8_t)(GS_POD_VALID | (e.counted ? GS_POD_COUNTED : 0u));
-        if (e.counted && e.mem) atomicAdd(&used[(size_t)e.node_idx * dev_stride + (uint32_t)e.dev], e.mem);
-    }
-    pods[e.slot] = now;
+                               int32_t* last_event, const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes,
+                               uint32_t dev_stride, unsigned long long* used) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) gs::event_apply<false>(i, ev, pods, n_slots, last_event, nodeinfo, n_nodes, dev_stride, used);
 }
 
 }  // namespace
@@ -124,7 +93,7 @@ int gs_pods_apply_static(int device, const gs_pod_event* d_events, uint32_t n_ev
     // the array still holds whatever the previous call (or an interrupted one) left: start from "no event"
     if (n_slots) k_static_clear<<<(n_slots + 255) / 256, 256, 0, st>>>(scratch, n_slots);
     const uint32_t blocks = (n_events + 255) / 256;
-    k_static_mark<<<blocks, 256, 0, st>>>(d_events, n_events, n_slots, scratch, d_nodeinfo, n_nodes);
+    k_static_mark<<<blocks, 256, 0, st>>>(d_events, n_events, n_slots, scratch, d_nodeinfo, n_nodes, dev_stride);
     k_static_apply<<<blocks, 256, 0, st>>>(d_events, n_events, d_pods, n_slots, scratch, d_nodeinfo, n_nodes, dev_stride,
                                            reinterpret_cast<unsigned long long*>(d_used));
     e = cudaGetLastError();

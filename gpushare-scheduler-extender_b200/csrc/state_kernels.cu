@@ -1,27 +1,20 @@
 // K1 (cache rebuild), K2 (incremental pod events) and K4 (ordered per-node binpack).
 #include "common.cuh"
 #include "kernels.h"
+#include "state_device.cuh"
+
+#include <algorithm>
 
 namespace gs {
 
 using u64 = unsigned long long;
 
-__device__ __forceinline__ gs_pod_record load_record(const gs_pod_record* p) {
-    static_assert(sizeof(gs_pod_record) == 16, "record is one 128-bit load");
-    uint4 v = *reinterpret_cast<const uint4*>(p);
-    gs_pod_record r;
-    *reinterpret_cast<uint4*>(&r) = v;
-    return r;
-}
-__device__ __forceinline__ void store_record(gs_pod_record* p, const gs_pod_record& r) {
-    *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(&r);
-}
-
-// a record may only name a device the node really has: nodeinfo.go:98-108 (`dev, found := n.devs[id]`)
-__device__ __forceinline__ bool legal_device(const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, uint32_t node,
-                                             int dev) {
-    if (node >= n_nodes || dev < 0) return false;
-    return (uint32_t)dev < nodeinfo_ndev(nodeinfo[node]);
+// zeroes used[] ahead of a rebuild; k_rebuild is launched as its programmatic dependent and reads its records
+// while this runs
+__global__ void __launch_bounds__(256) k_zero_u64x2(ulonglong2* d, size_t n2) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) d[i] = make_ulonglong2(0ull, 0ull);
 }
 
 __global__ void k_fill_i32(int32_t* d, int32_t v, size_t n) {
@@ -30,11 +23,11 @@ __global__ void k_fill_i32(int32_t* d, int32_t v, size_t n) {
 }
 
 __global__ void k_validate_records(gs_pod_record* pods, uint32_t first, uint32_t n, const uint32_t* __restrict__ nodeinfo,
-                                   uint32_t n_nodes) {
+                                   uint32_t n_nodes, uint32_t dev_stride) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     gs_pod_record r = load_record(pods + first + i);
-    if ((r.flags & GS_POD_VALID) && !legal_device(nodeinfo, n_nodes, r.node_idx, r.dev)) {
+    if ((r.flags & GS_POD_VALID) && !legal_device(nodeinfo, n_nodes, dev_stride, r.node_idx, r.dev)) {
         r.flags = 0;
         store_record(pods + first + i, r);
     }
@@ -72,6 +65,8 @@ k_rebuild(const gs_pod_record* __restrict__ pods, uint32_t n_slots, uint32_t dev
         recs[it].flags = 0;
         if (i < n_slots) recs[it] = load_record(pods + i);
     }
+    // used[] is being zeroed by the kernel before this one: nothing is added to it before that is complete
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 #pragma unroll
     for (int it = 0; it < kRebuildItems; ++it) {
         uint32_t bin = 0xffffffffu;
@@ -114,47 +109,17 @@ k_rebuild(const gs_pod_record* __restrict__ pods, uint32_t n_slots, uint32_t dev
 // its last effective event in the batch and additions commute mod 2^64, so: pass 1 finds the last
 // effective event per slot, pass 2 applies exactly those.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool event_effective(const gs_pod_event& e, uint32_t max_pods,
-                                                const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes) {
-    if (e.slot >= max_pods) return false;
-    if (e.op == GS_EV_REMOVE) return true;
-    return legal_device(nodeinfo, n_nodes, e.node_idx, e.dev);
-}
-
 __global__ void k_events_mark(const gs_pod_event* __restrict__ ev, uint32_t n, uint32_t max_pods, int32_t* last_ev,
-                              const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    gs_pod_event e = ev[i];
-    if (event_effective(e, max_pods, nodeinfo, n_nodes)) atomicMax(&last_ev[e.slot], (int32_t)i);
+                              const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, uint32_t dev_stride) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) event_mark(i, ev, max_pods, last_ev, nodeinfo, n_nodes, dev_stride);
 }
 
 __global__ void k_events_apply(const gs_pod_event* __restrict__ ev, uint32_t n, gs_pod_record* pods, uint32_t max_pods,
                                int32_t* last_ev, const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes,
                                uint32_t dev_stride, u64* used) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    gs_pod_event e = ev[i];
-    if (!event_effective(e, max_pods, nodeinfo, n_nodes)) return;
-    if (last_ev[e.slot] != (int32_t)i) return;
-    last_ev[e.slot] = -1;  // leave the scratch table idle for the next batch
-    gs_pod_record old = load_record(pods + e.slot);
-    if ((old.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED) && old.mem)
-        atomicAdd(&used[(size_t)old.node_idx * dev_stride + (uint32_t)old.dev], 0ull - old.mem);
-    gs_pod_record now;
-    now.mem = 0;
-    now.node_idx = 0;
-    now.dev = 0;
-    now.flags = 0;
-    now.pad_ = 0;
-    if (e.op == GS_EV_ADD) {
-        now.mem = e.mem;
-        now.node_idx = e.node_idx;
-        now.dev = e.dev;
-        now.flags = (uint8_t)(GS_POD_VALID | (e.counted ? GS_POD_COUNTED : 0u));
-        if (e.counted && e.mem) atomicAdd(&used[(size_t)e.node_idx * dev_stride + (uint32_t)e.dev], e.mem);
-    }
-    store_record(pods + e.slot, now);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) event_apply<true>(i, ev, pods, max_pods, last_ev, nodeinfo, n_nodes, dev_stride, used);  // re-arms the scratch
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -217,22 +182,25 @@ __global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, c
                 }
             }
         }
+        gs_pod_record old;
+        old.flags = 0;
+        if (cand >= 0 && b.slot < max_pods) {
+            old = load_record(pods + b.slot);
+            // A slot that holds an entry of ANOTHER node cannot be taken over here: that node's used[] row may be in
+            // the registers of the thread walking it, and a subtraction from here would be lost.  Refused, untouched.
+            if ((old.flags & GS_POD_VALID) && old.node_idx != node) cand = GS_BIND_SLOT_BUSY;
+        }
         out_dev[bi] = cand;
         if (cand >= 0 && b.slot < max_pods) {
-            gs_pod_record old = load_record(pods + b.slot);
             if ((old.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED) && old.mem) {
                 // the slot already held an entry (same UID bound again): replace, do not double count
-                if (old.node_idx == node) {
-                    if (kRegs) {
+                if (kRegs) {
 #pragma unroll
-                        for (int d = 0; d < 8; ++d)
-                            if (d == old.dev) reg[d] -= old.mem;
-                        dirty = true;
-                    } else {
-                        row[old.dev] -= old.mem;
-                    }
+                    for (int d = 0; d < 8; ++d)
+                        if (d == old.dev) reg[d] -= old.mem;
+                    dirty = true;
                 } else {
-                    atomicAdd(&used[(size_t)old.node_idx * dev_stride + (uint32_t)old.dev], 0ull - old.mem);
+                    row[old.dev] -= old.mem;
                 }
             }
             gs_pod_record now;
@@ -268,18 +236,41 @@ cudaError_t launch_fill_i32(int32_t* d, int32_t v, size_t n, cudaStream_t st) {
 }
 
 cudaError_t launch_validate_records(gs_pod_record* d_pods, uint32_t first, uint32_t n, const uint32_t* d_nodeinfo,
-                                    uint32_t n_nodes, cudaStream_t st) {
+                                    uint32_t n_nodes, uint32_t dev_stride, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    k_validate_records<<<(n + 255) / 256, 256, 0, st>>>(d_pods, first, n, d_nodeinfo, n_nodes);
+    k_validate_records<<<(n + 255) / 256, 256, 0, st>>>(d_pods, first, n, d_nodeinfo, n_nodes, dev_stride);
     return cudaGetLastError();
 }
 
-cudaError_t launch_rebuild(const gs_pod_record* d_pods, uint32_t n_slots, uint32_t dev_stride, u64* d_used,
-                           int /*sm_count*/, cudaStream_t st) {
+cudaError_t launch_rebuild(const gs_pod_record* d_pods, uint32_t n_slots, uint32_t n_node_rows, uint32_t dev_stride,
+                           u64* d_used, int sm_count, cudaStream_t st) {
+    // used[] has an even number of bytes / 16 only when rows * stride is even; the odd tail word is one more store
+    const size_t n_words = (size_t)n_node_rows * dev_stride;
+    if (n_words == 0) return cudaSuccess;
+    const size_t n2 = n_words / 2;
+    if (n_words & 1) {
+        cudaError_t e = cudaMemsetAsync(d_used + n_words - 1, 0, sizeof(u64), st);
+        if (e != cudaSuccess) return e;
+    }
+    if (n2) {
+        const unsigned blocks = (unsigned)std::min<size_t>((n2 + 255) / 256, (size_t)(sm_count > 0 ? sm_count : 148) * 8);
+        k_zero_u64x2<<<blocks, 256, 0, st>>>(reinterpret_cast<ulonglong2*>(d_used), n2);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
     if (n_slots == 0) return cudaSuccess;
     const uint32_t per_cta = kRebuildThreads * kRebuildItems;
-    k_rebuild<<<(n_slots + per_cta - 1) / per_cta, kRebuildThreads, 0, st>>>(d_pods, n_slots, dev_stride, d_used);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((n_slots + per_cta - 1) / per_cta);
+    cfg.blockDim = dim3(kRebuildThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, k_rebuild, d_pods, n_slots, dev_stride, d_used);
 }
 
 cudaError_t launch_apply_events(const gs_pod_event* d_events, uint32_t n, gs_pod_record* d_pods, uint32_t max_pods,
@@ -287,7 +278,7 @@ cudaError_t launch_apply_events(const gs_pod_event* d_events, uint32_t n, gs_pod
                                 uint32_t dev_stride, u64* d_used, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const uint32_t blocks = (n + 255) / 256;
-    k_events_mark<<<blocks, 256, 0, st>>>(d_events, n, max_pods, d_last_ev, d_nodeinfo, n_nodes);
+    k_events_mark<<<blocks, 256, 0, st>>>(d_events, n, max_pods, d_last_ev, d_nodeinfo, n_nodes, dev_stride);
     k_events_apply<<<blocks, 256, 0, st>>>(d_events, n, d_pods, max_pods, d_last_ev, d_nodeinfo, n_nodes, dev_stride,
                                            d_used);
     return cudaGetLastError();

@@ -13,6 +13,8 @@ PENDING, RUNNING, SUCCEEDED, FAILED, UNKNOWN = range(5)
 PASS, NOT_FOUND, NOT_SHARE, INSUFFICIENT = range(4)
 API_OK, API_CONFLICT_THEN_OK, API_CONFLICT_GET_FAILS, API_CONFLICT_TWICE, API_OTHER_ERROR, API_BIND_FAILS = range(6)
 
+API_HOOK = C.CFUNCTYPE(None, C.c_void_p, C.c_char_p, C.c_char_p, C.c_int)
+
 _lib = None
 
 
@@ -56,6 +58,8 @@ def lib():
         "gs_ext_ctrl_drain": (C.c_int, [vp]),
         "gs_ext_ctrl_queue_len": (sz, [vp]),
         "gs_ext_free": (None, [vp]),
+        "gs_ext_snapshot": (vp, [vp]),
+        "gs_ext_set_api_hook": (C.c_int, [vp, API_HOOK, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -72,7 +76,8 @@ EXPORTS = ["gs_ext_pod_new", "gs_ext_pod_free", "gs_ext_pod_set_node_name", "gs_
            "gs_ext_api_set_pod", "gs_ext_get_node_info", "gs_ext_build_cache", "gs_ext_add_or_update_pod",
            "gs_ext_remove_pod", "gs_ext_known_pod", "gs_ext_filter_json", "gs_ext_filter_codes", "gs_ext_bind",
            "gs_ext_inspect_node", "gs_ext_free", "gs_ext_informer_add", "gs_ext_informer_update",
-           "gs_ext_informer_delete", "gs_ext_ctrl_drain", "gs_ext_ctrl_queue_len"]
+           "gs_ext_informer_delete", "gs_ext_ctrl_drain", "gs_ext_ctrl_queue_len", "gs_ext_snapshot",
+           "gs_ext_set_api_hook"]
 
 
 def _b(s: str) -> bytes:
@@ -199,9 +204,24 @@ class Extender:
 
     def bind(self, pod_name, ns, uid, node, api_mode=API_OK):
         dev = C.c_int64(-1)
-        self._buf.value = b""
-        rc = lib().gs_ext_bind(self.h, _b(pod_name), _b(ns), _b(uid), _b(node), api_mode, C.byref(dev), self._buf, len(self._buf))
-        return dev.value, ("" if rc == 0 else self._buf.value.decode())
+        buf = C.create_string_buffer(2048)  # per call: binds may come from several threads
+        rc = lib().gs_ext_bind(self.h, _b(pod_name), _b(ns), _b(uid), _b(node), api_mode, C.byref(dev), buf, len(buf))
+        return dev.value, ("" if rc == 0 else buf.value.decode())
+
+    def set_api_hook(self, fn):
+        """fn(pod_key: str, node: str, api_mode: int) runs where Allocate's apiserver round trips happen (None = off)."""
+        if fn is None:
+            self._hook = API_HOOK(0)
+        else:
+            self._hook = API_HOOK(lambda user, key, node, mode: fn(key.decode(), node.decode(), mode))
+        lib().gs_ext_set_api_hook(self.h, self._hook, None)
+
+    @property
+    def launch_count(self) -> int:
+        """Kernels launched so far by the snapshot underneath."""
+        v = C.c_uint64()
+        capi._check(capi.load().gs_launch_count(C.c_void_p(lib().gs_ext_snapshot(self.h)), C.byref(v)))
+        return v.value
 
     def informer_add(self, pod: Pod):
         lib().gs_ext_informer_add(self.h, pod.h)

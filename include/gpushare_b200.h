@@ -26,9 +26,17 @@
  *
  * Conventions: every function returns GS_OK (0) or a negative GS_ERR_* code and never throws or
  * aborts; gs_last_error() gives the message for the calling thread.  Host buffers belong to the
- * caller and are only touched during the call (cgo's pointer rule).  Calls on one snapshot are
- * serialised by an internal lock; different snapshots (one per GPU) are independent.  Each call
- * makes the snapshot's device current for the calling thread.
+ * caller and are only touched during the call (cgo's pointer rule).  Each call makes the snapshot's
+ * device current for the calling thread.
+ *
+ * Threads: any thread may call any function.  The Filter entry points (gs_filter_batch*,
+ * gs_node_count) share the snapshot, as the reference's Filters share a node under RLock
+ * (pkg/cache/nodeinfo.go:116): host-buffer Filters of different threads run side by side, each in
+ * its own stream and work buffers.  Everything that changes the cluster state or reads it back
+ * (upsert, load, rebuild, events, binds, rollback, inspect, read_*) is exclusive, like Allocate and
+ * the pod events under the node's write lock (nodeinfo.go:72,90,141).  Different snapshots (one per
+ * GPU) are independent.  Work an entry point leaves running on a CUDA stream (the *_device and
+ * *_async calls) is ordered against later calls of the snapshot on the GPU, whatever stream they use.
  *
  * There is no CPU fallback: without a CUDA device gs_snapshot_create fails with GS_ERR_CUDA.
  */
@@ -42,7 +50,7 @@
 extern "C" {
 #endif
 
-#define GS_ABI_VERSION 1
+#define GS_ABI_VERSION 2
 
 enum {
     GS_OK = 0,
@@ -114,6 +122,7 @@ typedef struct gs_bind_req {
 
 #define GS_BIND_NO_DEVICE (-1)      /* allocateGPUID found nothing: "can't place the pod"        */
 #define GS_BIND_NODE_NOT_FOUND (-2) /* GetNodeInfo failed for node_idx                           */
+#define GS_BIND_SLOT_BUSY (-3)      /* `slot` holds an entry of another node: nothing was changed */
 
 typedef struct gs_snapshot gs_snapshot;
 
@@ -126,7 +135,9 @@ enum {
     GS_K_EXPAND = 4,
     GS_K_BIND_SORT = 5,
     GS_K_BIND_SCAN = 6,
-    GS_K_COUNT_ = 7
+    GS_K_COMPACT = 7,
+    GS_K_SUBSET = 8,
+    GS_K_COUNT_ = 9
 };
 
 const char* gs_last_error(void);
@@ -151,10 +162,17 @@ int gs_node_count(gs_snapshot* s, uint32_t* out_nodes);
  * stored invalid, as nodeinfo.go:98-108 would not add them.  Does not change used[]; follow with
  * gs_rebuild. */
 int gs_pods_load(gs_snapshot* s, const gs_pod_record* recs, uint32_t first_slot, uint32_t n);
-/* K1: used[node][dev] = sum of mem over valid, counted records (deviceinfo.go:41-54). */
+/* K1: used[node][dev] = sum of mem over valid, counted records (deviceinfo.go:41-54).  Reads every
+ * slot of the pod table (max_pods; slots never written are invalid), whatever wrote them. */
 int gs_rebuild(gs_snapshot* s);
-/* K2: AddOrUpdatePod / RemovePod deltas (cache.go:89-127). */
+/* K2: AddOrUpdatePod / RemovePod deltas (cache.go:89-127).  Returns when the events are applied. */
 int gs_pods_apply(gs_snapshot* s, const gs_pod_event* events, uint32_t n);
+/* The same, returning as soon as the batch is queued on the GPU (the events are copied before the call
+ * returns); every later call of the snapshot sees the batch applied.  This is how the informer's work
+ * queue (pkg/gpushare/controller.go:166-205) feeds the snapshot without stalling the Filter path.  A CUDA
+ * error of the batch surfaces in a later call.  gs_snapshot_sync waits for everything queued so far. */
+int gs_pods_apply_async(gs_snapshot* s, const gs_pod_event* events, uint32_t n);
+int gs_snapshot_sync(gs_snapshot* s);
 
 /* K3: the Predicate.Handler loop for a batch of pending pods against every node.
  * req[p] = uint(GetGPUMemoryFromPodResource(pod p)).  out_bitmap is [n_pods][row_stride_words]
@@ -170,6 +188,26 @@ int gs_filter_batch(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint32
  * ordered by the caller (they share the snapshot's work buffers). */
 int gs_filter_batch_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods,
                            uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream);
+/* K3 for the candidate list of one Filter request (`for _, nodeName := range *args.NodeNames`,
+ * pkg/scheduler/predicate.go:21): bit (c & 31) of word (c >> 5) of row p is the predicate of pod p on node
+ * node_subset[c].  An index that names no node of the snapshot, or a node that is not GS_NODE_OK, gives 0.
+ * row_stride_words >= ceil(n_candidates / 32); padding words are written as zero.  Only
+ * n_pods * ceil(n_candidates / 32) words cross PCIe, not a row of the whole cluster per pod. */
+int gs_filter_batch_subset(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, const uint32_t* node_subset,
+                           uint32_t n_candidates, uint32_t* out_bitmap, uint32_t row_stride_words);
+/* K3 in compact form.  The predicate is monotone in the request, so the [n_pods][nodes] answer is carried by
+ * one number per node and one per pod:
+ *     pass(p, n)  <=>  out_rank[(p / GS_MAX_BATCH) * rank_stride + n]  >=  out_cutoff[p]
+ * exactly, for every 64-bit request (rank[n] = how many requests of the chunk the node can hold, 0 for a node
+ * that can never pass; cutoff[p] = 1 + how many requests of the chunk are smaller than pod p's).  Ranks are
+ * relative to a chunk of GS_MAX_BATCH pods: out_rank is [ceil(n_pods / GS_MAX_BATCH)][rank_stride] with
+ * rank_stride >= node count (padding written as zero), out_cutoff is [n_pods].  2 bytes per node and per pod
+ * cross PCIe instead of one bit per (pod, node); the caller expands what it needs. */
+int gs_filter_batch_compact(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint16_t* out_rank,
+                            uint32_t rank_stride, uint16_t* out_cutoff);
+/* Same with device buffers, asynchronous on `cuda_stream` (padding of d_out_rank is left untouched). */
+int gs_filter_batch_compact_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods, uint16_t* d_out_rank,
+                                   uint32_t rank_stride, uint16_t* d_out_cutoff, void* cuda_stream);
 /* Profiling aid: launches only the K3 stages named in stage_mask (GS_STAGE_*), in order, on the
  * same buffers gs_filter_batch_device uses (n_pods <= GS_MAX_BATCH).  Later stages read what earlier
  * stages left in the snapshot's work buffers, so run the full set once first.  bench.py times each
@@ -184,7 +222,11 @@ int gs_node_classes(gs_snapshot* s, uint8_t* out_class, uint32_t n);
 
 /* K4: allocateGPUID + commit for a queue of binds, applied in array order per node
  * (nodeinfo.go:139-252).  out_dev[i] = chosen device, GS_BIND_NO_DEVICE or GS_BIND_NODE_NOT_FOUND.
- * A found bind commits used[node][dev] += commit_mem (when counted) and fills `slot`. */
+ * A found bind commits used[node][dev] += commit_mem (when counted) and fills `slot`.
+ * Slots: a slot may be named by one bind of the call only (GS_ERR_INVALID otherwise, nothing is run);
+ * a bind whose slot holds an entry of the SAME node replaces it (the same UID bound again,
+ * deviceinfo.go:63); a slot that holds an entry of another node is refused: out_dev[i] =
+ * GS_BIND_SLOT_BUSY, nothing changes (remove the entry first). */
 int gs_bind_batch(gs_snapshot* s, const gs_bind_req* binds, uint32_t n, int32_t* out_dev);
 /* Undo commits whose apiserver Update/Bind failed (nodeinfo.go:151-168,185-188: no commit). */
 int gs_bind_rollback(gs_snapshot* s, const uint32_t* slots, uint32_t n);
@@ -219,8 +261,15 @@ int gs_profile_read(gs_snapshot* s, int kernel_id, uint64_t* out_launches, doubl
 int gs_profile_reset(gs_snapshot* s);
 /* Total kernels this snapshot has launched since creation (always counted). */
 int gs_launch_count(gs_snapshot* s, uint64_t* out_launches);
+/* SMs the kernels size their grids for: those of the CUDA context that was current when the snapshot was
+ * created (fewer than the device has inside a green context or an MPS partition). */
+int gs_sm_count(gs_snapshot* s, int* out_sms);
 /* Device pointers of the snapshot arrays, for zero-copy use from the same process (tests, NCCL). */
 int gs_device_ptrs(gs_snapshot* s, void** d_used, void** d_capacity, void** d_nodeinfo, void** d_pods);
+/* Tell the snapshot that work queued on `cuda_stream` by the caller (a kernel of its own, gs_pods_apply_static)
+ * writes the arrays obtained from gs_device_ptrs: every later call of the snapshot is ordered behind that work,
+ * and a chain of overlapping filters (GS_OPT_PIPELINE_FILTERS) ends here. */
+int gs_snapshot_external_write(gs_snapshot* s, void* cuda_stream);
 
 /* Pod events for callers that must not allocate.  (No counterpart in the reference: this exists only
  * because some hosts of this library cannot call cudaMalloc.)
@@ -234,7 +283,10 @@ int gs_device_ptrs(gs_snapshot* s, void** d_used, void** d_capacity, void** d_no
  *   d_pods     [n_slots]             the pod table, updated in place
  *   d_nodeinfo [n_nodes]             one word per node: dev_count | (GS_NODE_* class << 16)
  *   d_used     [n_nodes][dev_stride] used memory per device, updated in place
- * (the arrays of a snapshot, from gs_device_ptrs, qualify).  The only scratch -- one int32 per pod slot
+ * (the arrays of a snapshot, from gs_device_ptrs, qualify: follow the call with gs_snapshot_external_write
+ * on the same stream so that the snapshot's own calls are ordered behind it).  An event takes effect only if
+ * it is a GS_EV_REMOVE, or a GS_EV_ADD onto a device index below both the node's dev_count and dev_stride;
+ * other op codes are skipped.  The only scratch -- one int32 per pod slot
  * -- is a fixed array of GS_STATIC_MAX_SLOTS entries (4 MiB) inside the library; every GPU that loads
  * the library holds it until the process exits.  n_slots above GS_STATIC_MAX_SLOTS is refused with
  * GS_ERR_CAPACITY.

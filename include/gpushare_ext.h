@@ -69,6 +69,8 @@ int64_t gs_ext_pod_resource_mem(const gs_ext_pod* p);       /* GetGPUMemoryFromP
 /* ---- the extender state: listers + cache mirror over one gs_snapshot ---- */
 int gs_ext_create(int device, uint32_t max_nodes, uint32_t max_devs, uint32_t max_pods, gs_ext** out);
 int gs_ext_destroy(gs_ext* x);
+/* the gs_snapshot underneath (gpushare_b200.h), e.g. for its launch and profile counters */
+struct gs_snapshot* gs_ext_snapshot(gs_ext* x);
 
 int gs_ext_node_lister_set(gs_ext* x, const char* name, int has_mem, int64_t mem, int has_count, int64_t count);
 int gs_ext_node_lister_delete(gs_ext* x, const char* name);
@@ -89,9 +91,15 @@ char* gs_ext_filter_json(gs_ext* x, const gs_ext_pod* pod, const char* const* no
 int gs_ext_filter_codes(gs_ext* x, const gs_ext_pod* const* pods, size_t n_pods, const char* const* node_names,
                         size_t n, uint8_t* codes);
 /* Bind.Handler: returns 0 when ExtenderBindingResult.Error would be "", else 1 with the message in err.
- * *dev_id receives allocateGPUID's choice (-1 = none). */
+ * *dev_id receives allocateGPUID's choice (-1 = none).  Binds to one node take turns (NodeInfo.rwmu,
+ * nodeinfo.go:141), binds to different nodes run side by side, the apiserver step included. */
 int gs_ext_bind(gs_ext* x, const char* pod_name, const char* pod_ns, const char* pod_uid, const char* node,
                 int api_mode, int64_t* dev_id, char* err, size_t errcap);
+/* The apiserver step of Allocate (Pods.Update + Pods.Bind, nodeinfo.go:150-184) is scripted by api_mode; a hook, if
+ * set, is called where those round trips happen, with only the node's lock held (tests use it to hold a bind
+ * inside the step and show that a bind to another node does not wait). */
+typedef void (*gs_ext_api_hook)(void* user, const char* pod_key, const char* node, int api_mode);
+int gs_ext_set_api_hook(gs_ext* x, gs_ext_api_hook hook, void* user);
 /* Inspect: per-device total/used of a cached node; returns gpu-count, or -1 with err. */
 int gs_ext_inspect_node(gs_ext* x, const char* name, uint64_t* total, uint64_t* used, int cap, char* err, size_t errcap);
 

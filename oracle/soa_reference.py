@@ -70,7 +70,9 @@ def pack_bitmap(passes: np.ndarray, stride_words: int) -> np.ndarray:
 
 def bind_sequential(binds, dev_capacity, used, dev_count, node_class, table=None):
     """allocateGPUID + commit in queue order (nodeinfo.go:139-252).  Mutates `used` (and `table`, the
-    pod-record array, when given).  Returns chosen devices (-1 none, -2 node not found)."""
+    pod-record array, when given).  Returns chosen devices (-1 none, -2 node not found, -3 the bind's slot
+    holds an entry of another node: an ABI rule of the device path, no counterpart in the reference, where a
+    committed pod is a fresh map entry)."""
     out = np.empty(len(binds), dtype=np.int32)
     M = (1 << 64) - 1
     for i in range(len(binds)):
@@ -87,6 +89,10 @@ def bind_sequential(binds, dev_capacity, used, dev_count, node_class, table=None
                 avail = (cap - int(used[n, d])) & M
                 if avail >= req and (cand == -1 or cand_mem > avail):
                     cand, cand_mem = d, avail
+        if cand >= 0 and table is not None:
+            old = table[int(b["slot"])]
+            if (old["flags"] & POD_VALID) and int(old["node_idx"]) != n:
+                cand = -3
         out[i] = cand
         if cand >= 0:
             if table is not None:
@@ -105,6 +111,8 @@ def apply_events(events, table, used, dev_count):
     for e in events:
         slot = int(e["slot"])
         if slot >= len(table):
+            continue
+        if e["op"] > 1:
             continue
         if e["op"] == 0:
             n, d = int(e["node_idx"]), int(e["dev"])

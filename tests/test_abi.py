@@ -50,7 +50,7 @@ def test_struct_layouts_match_header(tmp_path):
 
 def test_abi_version_and_no_cpu_fallback():
     lib = capi.load()
-    assert lib.gs_abi_version() == 1
+    assert lib.gs_abi_version() == 2
     import torch
     if not torch.cuda.is_available():
         with pytest.raises(gsx.GpushareError) as e:

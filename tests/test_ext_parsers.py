@@ -32,3 +32,21 @@ def test_pod_parsers_match_oracle():
         limits = [None if rng.random() < 0.2 else int(rng.integers(-5, 2**40)) for _ in range(rng.integers(0, 4))]
         a, b = X.Pod("p", annotations=ann, limits=limits), O.Pod("p", annotations=ann, limits=limits)
         assert (a.gpu_id, a.annotation_mem, a.resource_mem) == (b.gpu_id, b.annotation_mem, b.resource_mem), (ann, limits)
+
+
+def test_atoi_against_go_strconv_vectors():
+    """Both restatements of strconv.Atoi -- the oracle's and the product's -- against the rows of Go's own
+    strconv/atoi_test.go (tests/golden/atoi_vectors.json says where each row comes from)."""
+    import json
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "atoi_vectors.json")
+    doc = json.load(open(path))
+    n = 0
+    for table in ("parseInt64Tests", "parseUint64Tests_as_Atoi", "documented_behaviour"):
+        for row in doc[table]:
+            want = (row["value"], row["err"])
+            assert O.atoi(row["in"]) == want, ("oracle", table, row)
+            assert X.atoi(row["in"]) == want, ("product", table, row)
+            n += 1
+    assert n >= 30
