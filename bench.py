@@ -455,7 +455,7 @@ def strong_c4(args, gsx, torch, dist, tm, rank, world, local_rank, dev, reqs, pe
     g_rank = torch.zeros(world * sh.per_shard, dtype=torch.int16, device=dev)
     h_rank = torch.zeros(world * sh.per_shard, dtype=torch.int16).pin_memory()
     h_cut = torch.zeros(P, dtype=torch.int16).pin_memory()
-    stream = torch.cuda.current_stream(dev).cuda_stream
+    stream = torch.cuda.current_stream(dev).cuda_stream or 1  # (0 would mean the snapshot's own stream)
 
     def kernel(i):
         snap.filter_batch_device(d_req.data_ptr(), P, outs[i % N_OUT_BUFFERS].data_ptr(), stride, stream)

@@ -8,8 +8,11 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
+# development builds: GS_VARIANT=<name> builds and loads lib/libgpushare_b200_<name>.so (with GS_EXTRA_NVCC_FLAGS), so that
+# several compile-time variants of a kernel can be timed in one GPU session; the product is the unsuffixed library
+_VARIANT = os.environ.get("GS_VARIANT", "")
 LIB_DIR = os.path.join(HERE, "lib")
-LIB = os.path.join(LIB_DIR, "libgpushare_b200.so")
+LIB = os.path.join(LIB_DIR, "libgpushare_b200%s.so" % ("_" + _VARIANT if _VARIANT else ""))
 
 SOURCES = ["api.cu", "filter_kernels.cu", "state_kernels.cu", "compact_kernels.cu", "noalloc.cu", "ext.cpp"]
 HEADERS = ["common.cuh", "kernels.h", "state_device.cuh", "exports.map", "ext_state.inc", "ext_handlers.inc",
@@ -46,7 +49,7 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
     extra = os.environ.get("GS_EXTRA_NVCC_FLAGS", "").split()  # development builds only (e.g. -DGS_EXPAND_TRACE)
     objs = []
     for src in SOURCES:
-        obj = os.path.join(LIB_DIR, os.path.splitext(src)[0] + ".o")
+        obj = os.path.join(LIB_DIR, os.path.splitext(src)[0] + ("_" + _VARIANT if _VARIANT else "") + ".o")
         cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")

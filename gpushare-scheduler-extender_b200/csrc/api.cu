@@ -266,18 +266,20 @@ int alloc_ctx(gs_snapshot* s, FilterCtx& c) {
     CU(cudaMalloc(&c.d_row_bucket, 2 * B * sizeof(uint16_t)));
     CU(cudaMalloc(&c.d_pod_hist, 2 * 512 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_rank_planes, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t)));
+    CU(cudaMalloc(&c.d_low_planes, 2 * (size_t)s->rank_words * gs::kLowPlanes * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_node_key, 2 * (size_t)s->rank_words * 32 * sizeof(u64)));
     CU(cudaMalloc(&c.d_node_key32, 2 * (size_t)s->rank_words * 32 * sizeof(uint32_t)));
-    CU(cudaMalloc(&c.d_sched, 4 * sizeof(uint32_t)));
+    CU(cudaMalloc(&c.d_sched, 2 * gs::kSchedWords * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_epochs, 6 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_cpart, (size_t)gs::kCompactMaxSplits * B * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_csorted, B * sizeof(u64)));
     CU(cudaMalloc(&c.d_cdup, B * sizeof(uint32_t)));
     CU(cudaMemsetAsync(c.d_pod_hist, 0, 2 * 512 * sizeof(uint32_t), s->stream));
-    CU(cudaMemsetAsync(c.d_sched, 0, 4 * sizeof(uint32_t), s->stream));
+    CU(cudaMemsetAsync(c.d_sched, 0, 2 * gs::kSchedWords * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_epochs, 0, 6 * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_cdup, 0, B * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_rank_planes, 0, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t), s->stream));
+    CU(cudaMemsetAsync(c.d_low_planes, 0, 2 * (size_t)s->rank_words * gs::kLowPlanes * sizeof(uint32_t), s->stream));
     return GS_OK;
 }
 void free_ctx(FilterCtx& c) {
@@ -287,6 +289,7 @@ void free_ctx(FilterCtx& c) {
     cudaFree(c.d_row_bucket);
     cudaFree(c.d_pod_hist);
     cudaFree(c.d_rank_planes);
+    cudaFree(c.d_low_planes);
     cudaFree(c.d_node_key);
     cudaFree(c.d_node_key32);
     cudaFree(c.d_sched);
@@ -319,9 +322,10 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     fb.row_bucket = c.d_row_bucket + (size_t)set * GS_MAX_BATCH;
     fb.pod_hist = c.d_pod_hist + set * 512;
     fb.planes = c.d_rank_planes + (size_t)set * s->rank_words * gs::kRankPlanes;
+    fb.planes_low = c.d_low_planes + (size_t)set * s->rank_words * gs::kLowPlanes;
     fb.node_key = c.d_node_key + (size_t)set * s->rank_words * 32;
     fb.node_key32 = c.d_node_key32 + (size_t)set * s->rank_words * 32;
-    fb.sched = c.d_sched + set * 2;
+    fb.sched = c.d_sched + set * gs::kSchedWords;
     fb.set_index = set;
     fb.prep_done = c.d_epochs + 3 * set;
     fb.prep_epoch = c.d_epochs + 3 * set + 1;
@@ -339,6 +343,7 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     uint32_t bits = 0;
     while (bits < 64 && (s->max_capacity >> bits) != 0) ++bits;
     const uint32_t shift = bits > 9 ? bits - 9 : 0;
+    fb.shift = shift;
     int rc = GS_OK;
     const bool do_pods = (stages & GS_STAGE_SORT) != 0, do_nodes = (stages & GS_STAGE_NODE_RANK) != 0;
     if (do_pods || do_nodes)
@@ -351,8 +356,10 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     if (rc) return rc;
     if (stages & GS_STAGE_EXPAND)
         rc = timed(s, GS_K_EXPAND, st, 1, [&] {
-            cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, c.n_prep[set], st);
-            if (e == cudaSuccess) ++c.n_expand[set];
+            uint32_t epoch_step = 0;
+            cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, c.n_prep[set], st,
+                                              &epoch_step);
+            if (e == cudaSuccess) c.n_expand[set] += epoch_step;
             return e;
         });
     c.prev_filter = rc == GS_OK && stages == 7u && !s->profiling;
@@ -624,10 +631,13 @@ int gs_pods_apply(gs_snapshot* s, const gs_pod_event* events, uint32_t n) {
     if (n == 0) return GS_OK;
     rc = check_events(s, events, n);
     if (rc) return rc;
-    rc = grow_device(s, &s->d_stage, &s->d_stage_bytes, (size_t)n * sizeof(gs_pod_event), true);
+    const size_t ev_bytes = (size_t)n * sizeof(gs_pod_event);
+    rc = grow_device(s, &s->d_stage, &s->d_stage_bytes, ev_bytes, true);
     if (rc) return rc;
-    rc = w_h2d(s, s->d_stage, events, (size_t)n * sizeof(gs_pod_event));
+    rc = grow_pinned(s, &s->h_stage, &s->h_stage_bytes, ev_bytes);
     if (rc) return rc;
+    memcpy(s->h_stage, events, ev_bytes);  // (writers end synchronised: the staging is free when a call starts)
+    CU(cudaMemcpyAsync(s->d_stage, s->h_stage, ev_bytes, cudaMemcpyHostToDevice, s->stream));
     rc = timed(s, GS_K_APPLY, s->stream, 2, [&] {
         return gs::launch_apply_events(reinterpret_cast<const gs_pod_event*>(s->d_stage), n, s->d_pods, s->max_pods,
                                        s->d_last_ev, s->d_nodeinfo, s->n_nodes, s->max_devs, s->d_used, s->stream);
@@ -889,16 +899,22 @@ int gs_bind_batch(gs_snapshot* s, const gs_bind_req* binds, uint32_t n, int32_t*
         for (uint32_t i = 1; i < n; ++i)
             if (slots[i] == slots[i - 1]) return fail(GS_ERR_INVALID, "slot %u is named by more than one bind of the batch", slots[i]);
     }
+    // One pinned block holds the chunk's binds and its results: copy in, two kernels, copy out, ONE wait.  (Writers are
+    // exclusive and end synchronised, so the staging is free when a call starts.)
     for (uint32_t b0 = 0; b0 < n; b0 += GS_MAX_BATCH) {
         const uint32_t m = std::min<uint32_t>(GS_MAX_BATCH, n - b0);
         const size_t in_bytes = (size_t)m * sizeof(gs_bind_req);
         const size_t out_off = (in_bytes + 255) & ~(size_t)255;
-        rc = grow_device(s, &s->d_stage, &s->d_stage_bytes, out_off + (size_t)m * sizeof(int32_t), true);
+        const size_t out_bytes = (size_t)m * sizeof(int32_t);
+        rc = grow_device(s, &s->d_stage, &s->d_stage_bytes, out_off + out_bytes, true);
         if (rc) return rc;
+        rc = grow_pinned(s, &s->h_stage, &s->h_stage_bytes, out_off + out_bytes);
+        if (rc) return rc;
+        char* h = reinterpret_cast<char*>(s->h_stage);
         gs_bind_req* d_binds = reinterpret_cast<gs_bind_req*>(s->d_stage);
         int32_t* d_out = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(s->d_stage) + out_off);
-        rc = w_h2d(s, d_binds, binds + b0, in_bytes);
-        if (rc) return rc;
+        memcpy(h, binds + b0, in_bytes);
+        CU(cudaMemcpyAsync(d_binds, h, in_bytes, cudaMemcpyHostToDevice, s->stream));
         rc = timed(s, GS_K_BIND_SORT, s->stream, 1, [&] {
             return gs::launch_sort_binds(s->device, d_binds, m, s->d_bind_keys, s->d_bind_perm, s->stream);
         });
@@ -908,8 +924,9 @@ int gs_bind_batch(gs_snapshot* s, const gs_bind_req* binds, uint32_t n, int32_t*
                                         s->n_nodes, s->d_cap, s->max_devs, s->d_used, d_out, s->stream);
         });
         if (rc) return rc;
-        rc = w_d2h(s, out_dev + b0, d_out, (size_t)m * sizeof(int32_t));
-        if (rc) return rc;
+        CU(cudaMemcpyAsync(h + out_off, d_out, out_bytes, cudaMemcpyDeviceToHost, s->stream));
+        CU(cudaStreamSynchronize(s->stream));
+        memcpy(out_dev + b0, h + out_off, out_bytes);
     }
     return GS_OK;
 }

@@ -185,6 +185,14 @@ class ShardedCluster:
             self.engine.apply_events(mine)
 
 
+def _current_stream_handle(device) -> int:
+    """torch's current stream as a handle the C ABI takes.  The library reads a NULL stream as "the snapshot's own
+    stream", so torch's default stream (handle 0) is named explicitly: cudaStreamLegacy."""
+    import torch
+
+    return torch.cuda.current_stream(device).cuda_stream or 1
+
+
 class SnapshotEngine:
     """The product engine: a gsx.Snapshot on this rank's GPU (raises without CUDA: there is no CPU path).
     Filters read and write device memory only, on torch's current stream."""
@@ -202,8 +210,7 @@ class SnapshotEngine:
         if self._out is None or tuple(self._out.shape) != (P, stride_words):
             self._out = torch.zeros((P, stride_words), dtype=torch.int32, device=req.device)
         if P:
-            self.snap.filter_batch_device(req.data_ptr(), P, self._out.data_ptr(), stride_words,
-                                          torch.cuda.current_stream(req.device).cuda_stream)
+            self.snap.filter_batch_device(req.data_ptr(), P, self._out.data_ptr(), stride_words, _current_stream_handle(req.device))
         return self._out
 
     def filter_compact(self, req, rank_stride):
@@ -217,7 +224,7 @@ class SnapshotEngine:
             self._cutoff = torch.zeros(P, dtype=torch.int16, device=req.device)
         if P:
             self.snap.filter_batch_compact_device(req.data_ptr(), P, self._rank.data_ptr(), rank_stride, self._cutoff.data_ptr(),
-                                                  torch.cuda.current_stream(req.device).cuda_stream)
+                                                  _current_stream_handle(req.device))
         return self._rank, self._cutoff
 
     def bind(self, binds):

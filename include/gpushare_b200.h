@@ -184,8 +184,9 @@ int gs_snapshot_sync(gs_snapshot* s);
 int gs_filter_batch(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint32_t* out_bitmap,
                     uint32_t row_stride_words);
 /* Same, with req and out_bitmap in device memory of the snapshot's GPU; asynchronous on
- * `cuda_stream` (a cudaStream_t; NULL = the snapshot's own stream).  Calls on one snapshot must be
- * ordered by the caller (they share the snapshot's work buffers). */
+ * `cuda_stream` (a cudaStream_t; NULL = the snapshot's own stream -- to name CUDA's default stream pass
+ * cudaStreamLegacy or cudaStreamPerThread).  The device-buffer calls of one snapshot share one set of
+ * work buffers: the library orders them one after the other on the GPU, whatever streams they use. */
 int gs_filter_batch_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods,
                            uint32_t* d_out_bitmap, uint32_t row_stride_words, void* cuda_stream);
 /* K3 for the candidate list of one Filter request (`for _, nodeName := range *args.NodeNames`,
