@@ -266,20 +266,18 @@ int alloc_ctx(gs_snapshot* s, FilterCtx& c) {
     CU(cudaMalloc(&c.d_row_bucket, 2 * B * sizeof(uint16_t)));
     CU(cudaMalloc(&c.d_pod_hist, 2 * 512 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_rank_planes, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t)));
-    CU(cudaMalloc(&c.d_low_planes, 2 * (size_t)s->rank_words * gs::kLowPlanes * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_node_key, 2 * (size_t)s->rank_words * 32 * sizeof(u64)));
     CU(cudaMalloc(&c.d_node_key32, 2 * (size_t)s->rank_words * 32 * sizeof(uint32_t)));
-    CU(cudaMalloc(&c.d_sched, 2 * gs::kSchedWords * sizeof(uint32_t)));
+    CU(cudaMalloc(&c.d_sched, 4 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_epochs, 6 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_cpart, (size_t)gs::kCompactMaxSplits * B * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_csorted, B * sizeof(u64)));
     CU(cudaMalloc(&c.d_cdup, B * sizeof(uint32_t)));
     CU(cudaMemsetAsync(c.d_pod_hist, 0, 2 * 512 * sizeof(uint32_t), s->stream));
-    CU(cudaMemsetAsync(c.d_sched, 0, 2 * gs::kSchedWords * sizeof(uint32_t), s->stream));
+    CU(cudaMemsetAsync(c.d_sched, 0, 4 * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_epochs, 0, 6 * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_cdup, 0, B * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_rank_planes, 0, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t), s->stream));
-    CU(cudaMemsetAsync(c.d_low_planes, 0, 2 * (size_t)s->rank_words * gs::kLowPlanes * sizeof(uint32_t), s->stream));
     return GS_OK;
 }
 void free_ctx(FilterCtx& c) {
@@ -289,7 +287,6 @@ void free_ctx(FilterCtx& c) {
     cudaFree(c.d_row_bucket);
     cudaFree(c.d_pod_hist);
     cudaFree(c.d_rank_planes);
-    cudaFree(c.d_low_planes);
     cudaFree(c.d_node_key);
     cudaFree(c.d_node_key32);
     cudaFree(c.d_sched);
@@ -322,10 +319,9 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     fb.row_bucket = c.d_row_bucket + (size_t)set * GS_MAX_BATCH;
     fb.pod_hist = c.d_pod_hist + set * 512;
     fb.planes = c.d_rank_planes + (size_t)set * s->rank_words * gs::kRankPlanes;
-    fb.planes_low = c.d_low_planes + (size_t)set * s->rank_words * gs::kLowPlanes;
     fb.node_key = c.d_node_key + (size_t)set * s->rank_words * 32;
     fb.node_key32 = c.d_node_key32 + (size_t)set * s->rank_words * 32;
-    fb.sched = c.d_sched + set * gs::kSchedWords;
+    fb.sched = c.d_sched + set * 2;
     fb.set_index = set;
     fb.prep_done = c.d_epochs + 3 * set;
     fb.prep_epoch = c.d_epochs + 3 * set + 1;
@@ -343,7 +339,6 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     uint32_t bits = 0;
     while (bits < 64 && (s->max_capacity >> bits) != 0) ++bits;
     const uint32_t shift = bits > 9 ? bits - 9 : 0;
-    fb.shift = shift;
     int rc = GS_OK;
     const bool do_pods = (stages & GS_STAGE_SORT) != 0, do_nodes = (stages & GS_STAGE_NODE_RANK) != 0;
     if (do_pods || do_nodes)
@@ -356,10 +351,8 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     if (rc) return rc;
     if (stages & GS_STAGE_EXPAND)
         rc = timed(s, GS_K_EXPAND, st, 1, [&] {
-            uint32_t epoch_step = 0;
-            cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, c.n_prep[set], st,
-                                              &epoch_step);
-            if (e == cudaSuccess) c.n_expand[set] += epoch_step;
+            cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, c.n_prep[set], st);
+            if (e == cudaSuccess) ++c.n_expand[set];
             return e;
         });
     c.prev_filter = rc == GS_OK && stages == 7u && !s->profiling;

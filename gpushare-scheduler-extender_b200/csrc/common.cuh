@@ -23,16 +23,12 @@ constexpr uint32_t kUnsetNodeinfo = (uint32_t)GS_NODE_NOT_FOUND << 16;
 
 // Filter geometry.
 constexpr int kRankPlanes = 10;          // bit planes per 32-node word of the node bucket ids (0..513)
-constexpr int kLowPlanes = 10;           // bit planes of the key bits below the bucket scale (written when shift <= this)
 constexpr int kTileRows = 64;            // sorted pod rows per tile
 constexpr int kTileWords = 128;          // 32-bit words (4096 nodes) per tile
 constexpr int kExpandThreads = 256;
 
 // Column splits of the pairwise request count of the compact filter (compact_kernels.cu).
 constexpr uint32_t kCompactMaxSplits = 32;
-
-// Words of tile-scheduler state per K3 buffer set: 256 ticket counters + 256 finished-warp counters (k_expand_warp).
-constexpr uint32_t kSchedWords = 512;
 
 // Reader/writer lock of the snapshot with Go's sync.RWMutex rule: once a writer waits, new readers queue behind
 // it, so a stream of Filters cannot starve the pod events (pthread's default prefers readers).
@@ -91,10 +87,9 @@ struct FilterCtx {
     uint16_t* d_row_bucket = nullptr;             // [2][GS_MAX_BATCH]
     uint32_t* d_pod_hist = nullptr;               // [2][512] bucket counts (self re-arming)
     uint32_t* d_rank_planes = nullptr;            // [2][rank_words / kTileWords][kRankPlanes][kTileWords]
-    uint32_t* d_low_planes = nullptr;             // [2][rank_words / kTileWords][kLowPlanes][kTileWords]
     unsigned long long* d_node_key = nullptr;     // [2][rank_words * 32]
     uint32_t* d_node_key32 = nullptr;             // [2][rank_words * 32]
-    uint32_t* d_sched = nullptr;                  // [2][kSchedWords] tile scheduler of k_expand_warp (self re-arming)
+    uint32_t* d_sched = nullptr;                  // [2][2] tile scheduler of k_expand (self re-arming)
     uint32_t* d_epochs = nullptr;  // per set s: [3 * s] finished k_prep blocks, [3 * s + 1] k_prep epoch, [3 * s + 2] k_expand epoch
     uint32_t fb_set = 0;
     uint32_t n_prep[2] = {0, 0};      // what the set's k_prep / k_expand epochs will reach when everything issued has run

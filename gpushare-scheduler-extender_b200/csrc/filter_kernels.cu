@@ -14,8 +14,6 @@
 //              a word with 10 LOP3s; only nodes whose bucket lies inside the tile's own bucket range need
 //              the exact comparison.
 // (k_radix_sort, a stable single-CTA LSD radix sort, orders the bind queue by node for K4.)
-#include <stdlib.h>
-
 #include "common.cuh"
 #include "kernels.h"
 
@@ -340,25 +338,12 @@ __device__ __forceinline__ void prep_node_role(uint32_t block, const FilterBuffe
         uint32_t b = __ballot_sync(0xffffffffu, (q >> k) & 1u);
         if ((int)lane == k) mine = b;
     }
-    // The bits of the key below the bucket scale, bit-sliced too: bucket id and these bits together ARE the key of a
-    // node whose key lies below the open-ended last bucket, so tiles that need the exact test key >= req can do it
-    // on planes, without fetching keys (k_expand_warp).  Written when the scale leaves at most kLowPlanes bits.
-    const bool low_planes = shift <= (uint32_t)kLowPlanes;
-    if (low_planes) {
-#pragma unroll
-        for (int k = 0; k < kLowPlanes; ++k) {
-            uint32_t b = __ballot_sync(0xffffffffu, (uint32_t)k < shift && ((key >> k) & 1ull));
-            if ((int)lane == kRankPlanes + k) mine = b;
-        }
-    }
     may_write();
     if (word >= n_words) return;
     fb.node_key[node] = key;
     fb.node_key32[node] = key > 0xffffffffull ? 0xffffffffu : (uint32_t)key;  // exact against any request below 2^32
     if (lane < kRankPlanes)
         fb.planes[((size_t)(word / kTileWords) * kRankPlanes + lane) * kTileWords + (word % kTileWords)] = mine;
-    else if (low_planes && lane < kRankPlanes + kLowPlanes)
-        fb.planes_low[((size_t)(word / kTileWords) * kLowPlanes + (lane - kRankPlanes)) * kTileWords + (word % kTileWords)] = mine;
 }
 
 template <int kDevStride>
@@ -996,12 +981,6 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
     }
 }
 
-}  // namespace gs
-
-#include "expand_warp.cuh"
-
-namespace gs {
-
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
@@ -1057,7 +1036,7 @@ cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do
 
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
                           uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted,
-                          cudaStream_t st, uint32_t* grid_out) {
+                          cudaStream_t st) {
     if (n_pods == 0 || words == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
     {
         int dev = 0;
@@ -1078,42 +1057,6 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // overlap the launch with k_prep's tail
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    static const int impl = [] {
-        const char* e = getenv("GS_EXPAND_IMPL");  // development switch: "warp" = the warp-tile kernel, for A/B timing
-        return (e && e[0] == 'w') ? 1 : 0;
-    }();
-    if (impl == 1) {
-        // One warp per CTA, every CTA resident at once: a programmatic dependent (the next batch's k_prep) is launched
-        // only when ALL blocks of its primary have started.  24 one-warp CTAs per SM leave registers, warps and
-        // block slots for four k_prep blocks per SM beside them.
-        const uint32_t n_row_tiles = (n_pods + kWarpRows - 1) / kWarpRows;
-        const uint32_t n_tiles = n_col_blocks * n_row_tiles;
-        static const uint32_t per_sm = [] {
-            const char* e = getenv("GS_EXPAND_WARPS_PER_SM");
-            const int v = e ? atoi(e) : 0;
-            return (uint32_t)(v > 0 && v <= 65536 ? v : 24);
-        }();
-        // groups of warps with a ticket counter each: one group per SM (blocks i, i + n_groups, ... share an SM)
-        uint32_t n_groups = (uint32_t)sm_count < kSchedGroups ? (uint32_t)sm_count : kSchedGroups;
-        if (n_groups > n_tiles) n_groups = n_tiles;
-        uint32_t group_warps = (n_tiles + n_groups - 1) / n_groups;
-        if (group_warps > per_sm) group_warps = per_sm;
-        const uint32_t grid = n_groups * group_warps;
-        if (grid_out) *grid_out = grid;
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(grid);
-        cfg.blockDim = dim3(kExpandWarpThreads);
-        cfg.dynamicSmemBytes = 0;
-        cfg.stream = st;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        if (vec)
-            return cudaLaunchKernelEx(&cfg, k_expand_warp<true>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, n_tiles,
-                                      n_groups, group_warps, ov, prep_epoch_wanted);
-        return cudaLaunchKernelEx(&cfg, k_expand_warp<false>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, n_tiles,
-                                  n_groups, group_warps, ov, prep_epoch_wanted);
-    }
-    if (grid_out) *grid_out = 1;  // the CTA-tile kernel publishes once per launch
     const uint32_t n_row_tiles = (n_pods + kTileRows - 1) / kTileRows;
     const uint32_t n_tiles = n_col_blocks * n_row_tiles;
     // Four CTAs per SM stream as fast as five (tools/chunk_write_bw.cu), and the fifth slot's registers and

@@ -17,14 +17,12 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     uint16_t* row_bucket;             // [GS_MAX_BATCH] 1-based bucket of every grouped row
     uint32_t* pod_hist;               // [512] bucket counts of this buffer set (zero between launches)
     uint32_t* planes;                 // [words / kTileWords][kRankPlanes][kTileWords] node bucket ids, bit-sliced
-    uint32_t* planes_low;             // [words / kTileWords][kLowPlanes][kTileWords] key bits below the bucket scale, bit-sliced
-    uint32_t shift;                   // the bucket scale: bucket = min(value >> shift, 511)
     unsigned long long* node_key;     // [words * 32] max available memory per node
     uint32_t* node_key32;             // [words * 32] the same, saturated to 32 bits
-    uint32_t* sched;                  // [2 * 256] tile tickets and finished-warp counts per group of k_expand warps (self re-arming)
+    uint32_t* sched;                  // [2] tile scheduler of k_expand (self re-arming)
     uint32_t* prep_done;              // [1] finished blocks of the running k_prep (self re-arming)
     uint32_t* prep_epoch;             // [1] completed k_prep launches on this buffer set
-    uint32_t* expand_epoch;           // [1] finished k_expand warps on this buffer set, all launches together
+    uint32_t* expand_epoch;           // [1] completed k_expand launches on this buffer set
     uint32_t set_index;               // 0 / 1: which of the two buffer sets this is (development traces)
     unsigned int* fault;              // mapped host word: where a kernel gave up a bounded wait (may be null)
 };
@@ -34,10 +32,9 @@ cudaError_t launch_prep(const unsigned long long* d_req, uint32_t n_pods, bool d
                         const FilterBuffers& fb, const unsigned long long* d_used, const unsigned long long* d_cap,
                         const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words,
                         bool overlap_previous, uint32_t expand_epoch_wanted, cudaStream_t st);
-// *epoch_step: by how much the launch will advance fb.expand_epoch when it is over
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
                           uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted,
-                          cudaStream_t st, uint32_t* epoch_step);
+                          cudaStream_t st);
 
 // K1 / K2 / K4 (state_kernels.cu)
 cudaError_t launch_validate_records(gs_pod_record* d_pods, uint32_t first, uint32_t n, const uint32_t* d_nodeinfo,

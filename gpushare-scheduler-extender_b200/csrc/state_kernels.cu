@@ -82,11 +82,13 @@ k_rebuild(const gs_pod_record* __restrict__ pods, uint32_t n_slots, uint32_t dev
         const uint32_t prev = __shfl_up_sync(0xffffffffu, bin, 1);
         const bool head = (lane == 0) || (prev != bin);
         const uint32_t heads = __ballot_sync(0xffffffffu, head);
-        const uint32_t seg_start = 31u - __clz(heads & (0xffffffffu >> (31 - lane)));
+        if (heads != 0xffffffffu) {  // warp-uniform: a table in no particular order has no runs, and pays nothing for them
+            const uint32_t seg_start = 31u - __clz(heads & (0xffffffffu >> (31 - lane)));
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            u64 t = __shfl_up_sync(0xffffffffu, val, o);
-            if (lane >= seg_start + o) val += t;
+            for (int o = 1; o < 32; o <<= 1) {
+                u64 t = __shfl_up_sync(0xffffffffu, val, o);
+                if (lane >= seg_start + o) val += t;
+            }
         }
         const bool tail = (lane == 31) || ((heads >> (lane + 1)) & 1u);
         if (tail && bin != 0xffffffffu && val != 0) {

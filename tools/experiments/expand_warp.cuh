@@ -28,8 +28,13 @@
 
 namespace gs {
 
+#ifdef GS_WARP_ROWS_32
+constexpr int kWarpRows = 32;     // rows of a warp tile
+constexpr int kCntPlanes = 6;     // bit planes of a pass count 0..kWarpRows
+#else
 constexpr int kWarpRows = 16;     // rows of a warp tile
 constexpr int kCntPlanes = 5;     // bit planes of a pass count 0..kWarpRows
+#endif
 constexpr uint32_t kSchedGroups = 256;  // ticket counters per buffer set (>= the SM count)
 
 struct RowPair {                  // one row of the tile while it is being sorted
