@@ -270,7 +270,7 @@ int alloc_ctx(gs_snapshot* s, FilterCtx& c) {
     CU(cudaMalloc(&c.d_node_key32, 2 * (size_t)s->rank_words * 32 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_sched, 4 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_epochs, 6 * sizeof(uint32_t)));
-    CU(cudaMalloc(&c.d_cpart, (size_t)gs::kCompactMaxSplits * B * sizeof(uint32_t)));
+    CU(cudaMalloc(&c.d_cslices, (B + 1024) * sizeof(u64)));
     CU(cudaMalloc(&c.d_csorted, B * sizeof(u64)));
     CU(cudaMalloc(&c.d_cdup, B * sizeof(uint32_t)));
     CU(cudaMemsetAsync(c.d_pod_hist, 0, 2 * 512 * sizeof(uint32_t), s->stream));
@@ -291,7 +291,7 @@ void free_ctx(FilterCtx& c) {
     cudaFree(c.d_node_key32);
     cudaFree(c.d_sched);
     cudaFree(c.d_epochs);
-    cudaFree(c.d_cpart);
+    cudaFree(c.d_cslices);
     cudaFree(c.d_csorted);
     cudaFree(c.d_cdup);
     cudaFree(c.d_stage);
@@ -391,7 +391,7 @@ int compact_device_locked(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32
         uint32_t launched = 0;
         cudaError_t le = cudaSuccess;
         int rc = timed(s, GS_K_COMPACT, st, 0, [&] {
-            le = gs::launch_compact(d_req + p0, n, c.d_cpart, c.d_csorted, c.d_cdup, s->d_used, s->d_cap, s->d_nodeinfo,
+            le = gs::launch_compact(d_req + p0, n, c.d_cslices, c.d_csorted, c.d_cdup, s->d_used, s->d_cap, s->d_nodeinfo,
                                     s->n_nodes, s->max_devs, d_rank + (size_t)k * rank_stride, d_cutoff + p0, s->sm_count,
                                     st, &launched);
             return le;

@@ -27,8 +27,6 @@ constexpr int kTileRows = 64;            // sorted pod rows per tile
 constexpr int kTileWords = 128;          // 32-bit words (4096 nodes) per tile
 constexpr int kExpandThreads = 256;
 
-// Column splits of the pairwise request count of the compact filter (compact_kernels.cu).
-constexpr uint32_t kCompactMaxSplits = 32;
 
 // Reader/writer lock of the snapshot with Go's sync.RWMutex rule: once a writer waits, new readers queue behind
 // it, so a stream of Filters cannot starve the pod events (pthread's default prefers readers).
@@ -99,8 +97,8 @@ struct FilterCtx {
     const char* prev_out_lo = nullptr;   // ... writing [prev_out_lo, prev_out_hi)
     const char* prev_out_hi = nullptr;
 
-    // compact filter (rank / cutoff form): partial pair counts, sorted requests, duplicate counters
-    uint32_t* d_cpart = nullptr;                // [kCompactMaxSplits][GS_MAX_BATCH]
+    // compact filter (rank / cutoff form): requests sorted slice by slice, fully sorted requests, duplicate counters
+    unsigned long long* d_cslices = nullptr;    // [GS_MAX_BATCH rounded up to whole slices of 1024]
     unsigned long long* d_csorted = nullptr;    // [GS_MAX_BATCH]
     uint32_t* d_cdup = nullptr;                 // [GS_MAX_BATCH] zero between calls (self re-arming)
 

@@ -23,73 +23,94 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // ------------------------------------------------------------------------------------------------
-// compact, step 1: part[s][p] = #{ q in column slice s : req[q] < req[p] }.  All pairs, spread over
-// (row blocks x column slices) CTAs; a slice is staged in shared memory and every thread of the block
-// reads the same element at the same time (broadcast).  Requests below 2^32 -- all of them unless a
-// pod's limits sum to a negative number (pkg/cache/nodeinfo.go:217) -- compare as 32-bit values.
+// compact, step 1: the requests in slices of kSlice, each slice sorted by one CTA (bitonic network in shared
+// memory; the tail of the last slice is padded with all ones, which sorts behind every request).
 // ------------------------------------------------------------------------------------------------
-constexpr int kCountThreads = 256;
-constexpr uint32_t kCountChunk = 1024;  // columns staged at a time
+constexpr uint32_t kSlice = 1024;
+constexpr uint32_t kMaxSlices = (GS_MAX_BATCH + kSlice - 1) / kSlice;
 
-__global__ void __launch_bounds__(kCountThreads)
-k_req_count(const u64* __restrict__ req, uint32_t n_pods, uint32_t slice, uint32_t* __restrict__ part) {
-    __shared__ __align__(16) u64 col64[kCountChunk];
-    __shared__ __align__(16) uint32_t col32[kCountChunk];
+// one element per thread; exchanges at distances below 32 are shuffles, the fifteen at 32 and above go through
+// shared memory
+__global__ void __launch_bounds__(kSlice)
+k_slice_sort(const u64* __restrict__ req, uint32_t n_pods, u64* __restrict__ slices) {
+    __shared__ u64 v[kSlice];
     const uint32_t tid = threadIdx.x;
-    const uint32_t p = blockIdx.x * kCountThreads + tid;
-    const uint32_t c_begin = blockIdx.y * slice;
-    const uint32_t c_end = min(n_pods, c_begin + slice);
+    const uint32_t base = blockIdx.x * kSlice;
     pdl_launch_dependents();
-    const u64 mine = p < n_pods ? req[p] : 0ull;
-    uint32_t cnt = 0;
-    for (uint32_t c0 = c_begin; c0 < c_end; c0 += kCountChunk) {
-        const uint32_t len = min(kCountChunk, c_end - c0);
-        const uint32_t len4 = (len + 3u) & ~3u;
-        int big = (mine >> 32) != 0;
-        for (uint32_t i = tid; i < len4; i += kCountThreads) {
-            const u64 v = i < len ? req[c0 + i] : ~0ull;  // padding is never below anything
-            col64[i] = v;
-            col32[i] = (v >> 32) ? 0xffffffffu : (uint32_t)v;
-            big |= (i < len && (v >> 32) != 0);
-        }
-        const bool wide = __syncthreads_or(big) != 0;
-        if (!wide) {
-            const uint32_t m = (uint32_t)mine;
-            const uint4* c4 = reinterpret_cast<const uint4*>(col32);
-#pragma unroll 4
-            for (uint32_t i = 0; i < len4 / 4; ++i) {
-                const uint4 v = c4[i];
-                cnt += (v.x < m) + (v.y < m) + (v.z < m) + (v.w < m);
+    u64 mine = base + tid < n_pods ? req[base + tid] : ~0ull;
+    for (uint32_t k = 2; k <= kSlice; k <<= 1) {
+        const bool asc = (tid & k) == 0;
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            u64 other;
+            if (j >= 32) {
+                __syncthreads();  // everybody has read what the previous exchange left
+                v[tid] = mine;
+                __syncthreads();
+                other = v[tid ^ j];
+            } else {
+                other = __shfl_xor_sync(0xffffffffu, mine, j);
             }
-        } else {
-            const ulonglong2* c2 = reinterpret_cast<const ulonglong2*>(col64);
-#pragma unroll 4
-            for (uint32_t i = 0; i < len4 / 2; ++i) {
-                const ulonglong2 v = c2[i];
-                cnt += (v.x < mine) + (v.y < mine);
-            }
+            const bool lower = (tid & j) == 0;
+            // the lower index keeps the smaller value in an ascending block, the larger in a descending one
+            const bool take_min = lower == asc;
+            mine = take_min ? (other < mine ? other : mine) : (other > mine ? other : mine);
         }
-        __syncthreads();  // the next chunk overwrites the stage
     }
-    if (p < n_pods) part[(size_t)blockIdx.y * n_pods + p] = cnt;
+    slices[base + tid] = mine;
 }
 
-// compact, step 2: lt = sum of the partial counts; cutoff[p] = lt + 1; the request goes to position
-// lt + (arrival number among the pods with the same request) of the sorted array.  Equal requests have
-// equal lt and distinct requests distinct lt, so the duplicate counter of a value lives at dup[lt]; the
-// lanes of a warp that share a value go to it as one atomic.
-__global__ void __launch_bounds__(256)
-k_req_place(const u64* __restrict__ req, uint32_t n_pods, uint32_t splits, const uint32_t* __restrict__ part,
+// compact, step 2: lt[p] = #{q : req[q] < req[p]} = the sum over the sorted slices of a lower bound (the searches
+// of a thread are independent chains of eleven loads from L1/L2); cutoff[p] = lt + 1; the request goes to position
+// lt + (arrival number among the pods with the same request) of the fully sorted array.  Equal requests have equal
+// lt and distinct requests distinct lt, so the duplicate counter of a value lives at dup[lt]; the lanes of a warp
+// that share a value go to it as one atomic.
+__global__ void __launch_bounds__(64)
+k_req_place(const u64* __restrict__ req, uint32_t n_pods, uint32_t n_slices, const u64* __restrict__ g_slices,
             uint32_t* __restrict__ dup, u64* __restrict__ sorted, uint16_t* __restrict__ cutoff) {
+    extern __shared__ __align__(16) u64 slices[];  // every block keeps all the slices at hand: the searches are dependent loads
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31;
     pdl_launch_dependents();
     const u64 mine = p < n_pods ? req[p] : 0ull;
-    pdl_wait();  // the partial counts
+    pdl_wait();  // the sorted slices
+    {
+        // one bulk asynchronous copy (TMA) per slice, all in flight together, completion on an mbarrier
+        __shared__ __align__(8) uint64_t bar;
+        const uint32_t bar_addr = (uint32_t)__cvta_generic_to_shared(&bar);
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(n_slices * kSlice * 8u) : "memory");
+            for (uint32_t sl = 0; sl < n_slices; ++sl)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                 (uint32_t)__cvta_generic_to_shared(slices + sl * kSlice)),
+                             "l"(g_slices + sl * kSlice), "r"(kSlice * 8u), "r"(bar_addr)
+                             : "memory");
+        }
+        __syncthreads();  // the barrier is initialised before anybody waits on it
+        uint32_t done = 0;
+        while (!done)
+            asm volatile(
+                "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}\n"
+                : "=r"(done)
+                : "r"(bar_addr)
+                : "memory");
+    }
     uint32_t lt = 0xffffff00u + lane;  // idle lanes: a group of their own
     if (p < n_pods) {
+        uint32_t pos[kMaxSlices];
+#pragma unroll
+        for (uint32_t s = 0; s < kMaxSlices; ++s) pos[s] = 0;
+#pragma unroll
+        for (uint32_t step = kSlice / 2; step > 0; step >>= 1) {
+#pragma unroll
+            for (uint32_t s = 0; s < kMaxSlices; ++s)
+                if (s < n_slices && slices[s * kSlice + pos[s] + step - 1] < mine) pos[s] += step;
+        }
         lt = 0;
-        for (uint32_t s = 0; s < splits; ++s) lt += part[(size_t)s * n_pods + p];
+#pragma unroll
+        for (uint32_t s = 0; s < kMaxSlices; ++s)
+            if (s < n_slices) lt += pos[s] + (slices[s * kSlice + pos[s]] < mine ? 1u : 0u);
     }
     const uint32_t same = __match_any_sync(0xffffffffu, lt);
     const uint32_t leader = __ffs(same) - 1;
@@ -156,22 +177,12 @@ k_filter_subset(const u64* __restrict__ req, uint32_t n_pods, const uint32_t* __
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
-uint32_t compact_splits(uint32_t n_pods, int sm_count) {
-    const uint32_t row_blocks = (n_pods + kCountThreads - 1) / kCountThreads;
-    if (row_blocks == 0) return 1;
-    uint32_t want = (4u * (uint32_t)(sm_count > 0 ? sm_count : 1) + row_blocks - 1) / row_blocks;
-    if (want < 1) want = 1;
-    if (want > kCompactMaxSplits) want = kCompactMaxSplits;
-    if (want > n_pods) want = n_pods;
-    return want;
-}
-
 template <class... Params, class... Args>
-static cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+static cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // the launch itself overlaps the predecessor's tail
@@ -181,27 +192,36 @@ static cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, 
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
 }
 
-cudaError_t launch_compact(const u64* d_req, uint32_t n_pods, uint32_t* d_part, u64* d_sorted, uint32_t* d_dup,
+cudaError_t launch_compact(const u64* d_req, uint32_t n_pods, u64* d_slices, u64* d_sorted, uint32_t* d_dup,
                            const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo, uint32_t n_nodes,
                            uint32_t dev_stride, uint16_t* d_rank, uint16_t* d_cutoff, int sm_count, cudaStream_t st,
                            uint32_t* n_launches) {
     *n_launches = 0;
     if (n_pods == 0 || n_pods > GS_MAX_BATCH) return cudaErrorInvalidValue;
-    const uint32_t splits = compact_splits(n_pods, sm_count);
-    const uint32_t slice = ((n_pods + splits - 1) / splits + 3u) & ~3u;
-    const uint32_t row_blocks = (n_pods + kCountThreads - 1) / kCountThreads;
+    (void)sm_count;
+    const uint32_t n_slices = (n_pods + kSlice - 1) / kSlice;
     // the first kernel of the chain is an ordinary launch: it waits for everything before it in the stream
-    k_req_count<<<dim3(row_blocks, (n_pods + slice - 1) / slice), kCountThreads, 0, st>>>(d_req, n_pods, slice, d_part);
+    static bool attrs_done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attrs_done[dev]) {
+        const int max_smem = (int)(kMaxSlices * kSlice * sizeof(u64));  // 96 KB: all slices
+        cudaError_t ea = cudaFuncSetAttribute(k_req_place, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (ea != cudaSuccess) return ea;
+        if (dev >= 0 && dev < 64) attrs_done[dev] = true;
+    }
+    k_slice_sort<<<n_slices, kSlice, 0, st>>>(d_req, n_pods, d_slices);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     ++*n_launches;
-    e = launch_pdl(k_req_place, dim3((n_pods + 255) / 256), dim3(256), st, d_req, n_pods, (n_pods + slice - 1) / slice,
-                   (const uint32_t*)d_part, d_dup, d_sorted, d_cutoff);
+    // small blocks: the searches of a pod are latency, so they are spread over as many SMs as there are blocks
+    e = launch_pdl(k_req_place, dim3((n_pods + 63) / 64), dim3(64), (size_t)n_slices * kSlice * sizeof(u64), st, d_req, n_pods,
+                   n_slices, (const u64*)d_slices, d_dup, d_sorted, d_cutoff);
     if (e != cudaSuccess) return e;
     ++*n_launches;
     const uint32_t n_threads = n_nodes > n_pods ? n_nodes : n_pods;
-    e = launch_pdl(k_node_rank, dim3((n_threads + 255) / 256), dim3(256), st, (const u64*)d_sorted, n_pods, d_dup, d_used,
-                   d_cap, d_nodeinfo, n_nodes, dev_stride, d_rank);
+    e = launch_pdl(k_node_rank, dim3((n_threads + 255) / 256), dim3(256), 0, st, (const u64*)d_sorted,
+                   n_pods, d_dup, d_used, d_cap, d_nodeinfo, n_nodes, dev_stride, d_rank);
     if (e != cudaSuccess) return e;
     ++*n_launches;
     return cudaSuccess;

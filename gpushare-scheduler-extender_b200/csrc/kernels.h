@@ -52,11 +52,9 @@ cudaError_t launch_bind_scan(const gs_bind_req* d_binds, uint32_t n, const unsig
 cudaError_t launch_fill_i32(int32_t* d, int32_t v, size_t n, cudaStream_t st);
 
 // compact and candidate-list forms of K3 (compact_kernels.cu)
-// Splits the pairwise count of n_pods requests into column slices; returns the number of slices used.
-uint32_t compact_splits(uint32_t n_pods, int sm_count);
 // rank[n] = #{p : req[p] <= key[n]} (0 for a node that can never pass), cutoff[p] = 1 + #{q : req[q] < req[p]}:
 // pass(p, n) <=> rank[n] >= cutoff[p].  Three launches; returns how many were made through *n_launches.
-cudaError_t launch_compact(const unsigned long long* d_req, uint32_t n_pods, uint32_t* d_part, unsigned long long* d_sorted,
+cudaError_t launch_compact(const unsigned long long* d_req, uint32_t n_pods, unsigned long long* d_slices, unsigned long long* d_sorted,
                            uint32_t* d_dup, const unsigned long long* d_used, const unsigned long long* d_cap,
                            const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint16_t* d_rank,
                            uint16_t* d_cutoff, int sm_count, cudaStream_t st, uint32_t* n_launches);

@@ -54,8 +54,10 @@ for k in range(2):
                           rng.choice(synth.CATALOGUE[:6], 1000))
     snap.pods_apply(ev)
 bits = gsx.unpack_bitmap(outs[0][:2048].cpu().numpy().view(np.uint32), N)
-first = bits.argmax(axis=1)
-ok = bits.any(axis=1)
+cnt = bits.sum(axis=1)
+ok = cnt > 0
+pick = np.arange(2048, dtype=np.int64) * 2654435761 % np.maximum(cnt, 1)      # a pseudo-random passing node per pod
+first = (np.cumsum(bits, axis=1) > pick[:, None]).argmax(axis=1)
 binds = synth.bind_records(first[ok], reqs[:2048][ok].view(np.int64), first_slot=sc.n_pods + 4000)
 got = snap.bind_batch(binds)
 print("profile driver ok:", int((got >= 0).sum()), "binds placed;", snap.launch_count, "launches")
