@@ -36,73 +36,61 @@ __global__ void k_validate_records(gs_pod_record* pods, uint32_t first, uint32_t
 // ------------------------------------------------------------------------------------------------
 // K1: used[node][dev] = sum of mem over valid, counted records (pkg/cache/deviceinfo.go:41-54 as a
 // segmented integer reduction).  Each warp reduces runs of equal (node, dev) with shuffles, so a pod
-// table grouped by node issues one atomic per run; run totals go to a shared-memory window of bins
-// anchored at the CTA's first record and only what falls outside it goes straight to global atomics.
+// table grouped by (node, device) issues one atomic per run; everything else is one 64-bit RED per record.
 // ------------------------------------------------------------------------------------------------
 constexpr int kRebuildThreads = 256;
-constexpr int kRebuildItems = 8;           // records per thread
-constexpr uint32_t kRebuildWindow = 2048;  // bins privatised per CTA (16 KB)
+constexpr int kRebuildItems = 4;           // records per thread and chunk
+constexpr uint32_t kRebuildChunk = kRebuildThreads * kRebuildItems;
 
+// Persistent: a CTA walks chunks blockIdx.x, blockIdx.x + gridDim.x, ... and loads the next chunk's records before it
+// works on the current one, so record loads and atomics of different chunks overlap all the way through.
+// (A shared-memory window of privatised bins per CTA, which round 1 had, lost to plain global atomics for every table
+// order measured -- random slots, slots grouped by node, slots sorted by (node, device): 64-bit shared-memory
+// atomics are compare-and-swap loops -- and is gone; profiles/NOTES.md.)
 __global__ void __launch_bounds__(kRebuildThreads)
 k_rebuild(const gs_pod_record* __restrict__ pods, uint32_t n_slots, uint32_t dev_stride, u64* __restrict__ used) {
-    __shared__ u64 win[kRebuildWindow];
-    __shared__ uint32_t win_base;
     const uint32_t tid = threadIdx.x, lane = tid & 31;
-    const uint32_t cta_first = blockIdx.x * (kRebuildThreads * kRebuildItems);
-    for (uint32_t i = tid; i < kRebuildWindow; i += kRebuildThreads) win[i] = 0;
-    if (tid == 0) {
-        gs_pod_record r0 = load_record(pods + cta_first);
-        win_base = r0.node_idx * dev_stride;  // any anchor is correct; this one suits node-grouped tables
-    }
-    __syncthreads();
-    const uint32_t base = win_base;
+    const uint32_t n_chunks = (n_slots + kRebuildChunk - 1) / kRebuildChunk;
 
-    // all of the thread's records first (independent 16-byte loads in flight together), the arithmetic after
-    gs_pod_record recs[kRebuildItems];
+    auto load_chunk = [&](uint32_t chunk, gs_pod_record (&r)[kRebuildItems]) {
 #pragma unroll
-    for (int it = 0; it < kRebuildItems; ++it) {
-        const uint32_t i = cta_first + it * kRebuildThreads + tid;
-        recs[it].flags = 0;
-        if (i < n_slots) recs[it] = load_record(pods + i);
-    }
+        for (int it = 0; it < kRebuildItems; ++it) {
+            const uint32_t i = chunk * kRebuildChunk + it * kRebuildThreads + tid;
+            r[it].flags = 0;
+            if (chunk < n_chunks && i < n_slots) r[it] = load_record(pods + i);
+        }
+    };
+    gs_pod_record recs[kRebuildItems], next[kRebuildItems];
+    load_chunk(blockIdx.x, recs);
     // used[] is being zeroed by the kernel before this one: nothing is added to it before that is complete
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    for (uint32_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        load_chunk(chunk + gridDim.x, next);
 #pragma unroll
-    for (int it = 0; it < kRebuildItems; ++it) {
-        uint32_t bin = 0xffffffffu;
-        u64 val = 0;
-        {
+        for (int it = 0; it < kRebuildItems; ++it) {
             const gs_pod_record r = recs[it];
+            uint32_t bin = 0xffffffffu;
+            u64 val = 0;
             if ((r.flags & (GS_POD_VALID | GS_POD_COUNTED)) == (GS_POD_VALID | GS_POD_COUNTED)) {
                 bin = r.node_idx * dev_stride + (uint32_t)r.dev;
                 val = r.mem;
             }
-        }
-        // segmented inclusive scan over runs of equal bins
-        const uint32_t prev = __shfl_up_sync(0xffffffffu, bin, 1);
-        const bool head = (lane == 0) || (prev != bin);
-        const uint32_t heads = __ballot_sync(0xffffffffu, head);
-        if (heads != 0xffffffffu) {  // warp-uniform: a table in no particular order has no runs, and pays nothing for them
-            const uint32_t seg_start = 31u - __clz(heads & (0xffffffffu >> (31 - lane)));
+            // segmented inclusive scan over runs of equal bins: one atomic per run and warp
+            const uint32_t prev = __shfl_up_sync(0xffffffffu, bin, 1);
+            const uint32_t heads = __ballot_sync(0xffffffffu, (lane == 0) || (prev != bin));
+            if (heads != 0xffffffffu) {  // warp-uniform: a table in no particular order has no runs, and pays nothing for them
+                const uint32_t seg_start = 31u - __clz(heads & (0xffffffffu >> (31 - lane)));
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                u64 t = __shfl_up_sync(0xffffffffu, val, o);
-                if (lane >= seg_start + o) val += t;
+                for (int o = 1; o < 32; o <<= 1) {
+                    u64 t = __shfl_up_sync(0xffffffffu, val, o);
+                    if (lane >= seg_start + o) val += t;
+                }
             }
+            const bool tail = (lane == 31) || ((heads >> (lane + 1)) & 1u);
+            if (tail && bin != 0xffffffffu && val != 0) atomicAdd(&used[bin], val);
         }
-        const bool tail = (lane == 31) || ((heads >> (lane + 1)) & 1u);
-        if (tail && bin != 0xffffffffu && val != 0) {
-            const uint32_t rel = bin - base;
-            if (rel < kRebuildWindow)
-                atomicAdd(&win[rel], val);
-            else
-                atomicAdd(&used[bin], val);
-        }
-    }
-    __syncthreads();
-    for (uint32_t i = tid; i < kRebuildWindow; i += kRebuildThreads) {
-        u64 v = win[i];
-        if (v) atomicAdd(&used[base + i], v);
+#pragma unroll
+        for (int it = 0; it < kRebuildItems; ++it) recs[it] = next[it];
     }
 }
 
@@ -261,9 +249,10 @@ cudaError_t launch_rebuild(const gs_pod_record* d_pods, uint32_t n_slots, uint32
         if (e != cudaSuccess) return e;
     }
     if (n_slots == 0) return cudaSuccess;
-    const uint32_t per_cta = kRebuildThreads * kRebuildItems;
+    const uint32_t n_chunks = (n_slots + kRebuildChunk - 1) / kRebuildChunk;
+    const uint32_t resident = (uint32_t)(sm_count > 0 ? sm_count : 148) * 4;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((n_slots + per_cta - 1) / per_cta);
+    cfg.gridDim = dim3(n_chunks < resident ? n_chunks : resident);
     cfg.blockDim = dim3(kRebuildThreads);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = st;
