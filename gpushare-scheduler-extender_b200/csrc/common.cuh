@@ -23,7 +23,8 @@ constexpr uint32_t kUnsetNodeinfo = (uint32_t)GS_NODE_NOT_FOUND << 16;
 
 // Filter geometry.
 constexpr int kRankPlanes = 10;          // bit planes per 32-node word of the node bucket ids (0..513)
-constexpr int kTileRows = 64;            // sorted pod rows per tile
+constexpr int kTileRows = 64;            // sorted pod rows per tile (32: 18.3 us alone, 128: 20.5 us; profiles/NOTES.md 27)
+constexpr int kDensePlanes = 7;          // bit planes of a pass count 0..kTileRows
 constexpr int kTileWords = 128;          // 32-bit words (4096 nodes) per tile
 constexpr int kExpandThreads = 256;
 

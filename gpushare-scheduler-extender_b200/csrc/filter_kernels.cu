@@ -842,11 +842,11 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             if (!((sm.somew[t[u]] >> lane) & 1u)) c = 0;
                             uint32_t mine = 0;
 #pragma unroll
-                            for (int q = 0; q < 7; ++q) {
+                            for (int q = 0; q < kDensePlanes; ++q) {
                                 const uint32_t bal = __ballot_sync(0xffffffffu, (c >> q) & 1u);
                                 if ((int)lane == q) mine = bal;
                             }
-                            if (lane < 7) sm.cntp[lane * kTileWords + t[u]] = mine;
+                            if (lane < kDensePlanes) sm.cntp[lane * kTileWords + t[u]] = mine;
                         }
                     }
                     __syncthreads();  // counts complete; the key area may be overwritten
@@ -904,7 +904,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             const uint32_t thr = rr + 1;
                             uint4 ge = make_uint4(~0u, ~0u, ~0u, ~0u);
 #pragma unroll
-                            for (int q = 0; q < 7; ++q) {
+                            for (int q = 0; q < kDensePlanes; ++q) {
                                 const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lcol * 4]);
                                 if ((thr >> q) & 1u) {
                                     ge.x &= pl.x; ge.y &= pl.y; ge.z &= pl.z; ge.w &= pl.w;
@@ -943,7 +943,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                                 const uint32_t thr = rr + 1;
                                 v = ~0u;
 #pragma unroll
-                                for (int q = 0; q < 7; ++q) {
+                                for (int q = 0; q < kDensePlanes; ++q) {
                                     const uint32_t pl = sm.cntp[q * kTileWords + wl];
                                     v = ((thr >> q) & 1u) ? (v & pl) : (v | pl);
                                 }
@@ -995,6 +995,11 @@ static cudaError_t ensure_attrs(int device) {
     e = cudaFuncSetAttribute(k_expand<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_expand<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    // static shared memory + the occupancy pad may exceed the 48 KB a kernel gets without asking
+    e = cudaFuncSetAttribute(k_expand<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_expand<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384);
     if (e != cudaSuccess) return e;
     if (device >= 0 && device < 64) g_attr_done[device] = true;
     return cudaSuccess;

@@ -4,9 +4,9 @@ import sys,json
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])
 print('$1', 'step %.2f [%.2f %.2f]' % (1e3*d['ms_per_step_spread']['median'], 1e3*d['ms_per_step_spread']['min'], 1e3*d['ms_per_step_spread']['max']), 'expand %.2f prep %.2f' % (1e3*d['kernel_ms']['expand'], 1e3*d['kernel_ms']['prep']), 'frac %.3f step_frac %.3f' % (d['roofline']['frac'], d['roofline']['step_frac']))"
 }
-export GS_EXPAND_IMPL=warp GS_VARIANT=rows32
-timeout 300 python -m pytest tests/test_gpu_filter.py -m gpu -q -x --timeout 300 -p no:cacheprovider 2>&1 | tail -3
-for w in 6 8 12 16; do
-  export GS_EXPAND_WARPS_PER_SM=$w
-  run "variant=[rows32] warps/SM=$w"
+for v in $VARIANTS; do
+  export GS_VARIANT=$v
+  [ "$v" = base ] && export GS_VARIANT=""
+  timeout 300 python -m pytest tests/test_gpu_filter.py -m gpu -q -x --timeout 300 -p no:cacheprovider 2>&1 | tail -1
+  run "variant=[$v]"
 done
