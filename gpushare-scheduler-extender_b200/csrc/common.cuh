@@ -26,7 +26,7 @@ constexpr int kRankPlanes = 10;          // bit planes per 32-node word of the n
 constexpr int kTileRows = 64;            // sorted pod rows per tile (32: 18.3 us alone, 128: 20.5 us; profiles/NOTES.md 27)
 constexpr int kDensePlanes = 7;          // bit planes of a pass count 0..kTileRows
 constexpr int kTileWords = 128;          // 32-bit words (4096 nodes) per tile
-constexpr int kExpandThreads = 256;
+constexpr int kExpandThreads = 256;         // (128-thread CTAs, 4-6 per SM: 20-22 us alone; profiles/NOTES.md 28)
 
 
 // Reader/writer lock of the snapshot with Go's sync.RWMutex rule: once a writer waits, new readers queue behind

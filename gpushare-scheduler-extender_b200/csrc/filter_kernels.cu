@@ -597,14 +597,14 @@ __device__ unsigned long long g_trace[148 * 5 * kTraceTiles * kTraceSlots];
 #endif
 
 template <bool kVec>
-__global__ void __launch_bounds__(kExpandThreads, 5)
+__global__ void __launch_bounds__(kExpandThreads, kExpandThreads == 256 ? 5 : 8)
 k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_stride, uint32_t* __restrict__ out,
          uint32_t n_col_blocks, uint32_t inv_col_blocks, uint32_t n_tiles, uint32_t overlap_previous,
          uint32_t prep_epoch_wanted) {
     __shared__ __align__(128) ExpandSmem sm;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr uint32_t kWarps = kExpandThreads / 32;
-    static_assert(kExpandThreads >= kTileWords + kTileRows, "phase A: one thread per word, one per row");
+    static_assert(kExpandThreads >= kTileWords && kExpandThreads >= kTileRows, "phase A: one thread per word, one per row");
     const uint32_t* __restrict__ planes = fb.planes;
 
     __shared__ TileInputs tin[kPrefetch];
@@ -697,8 +697,11 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                 if (__popc(pm) > kSparseMax) sm.n_heavy = 1u;
             }
             sm.pidx[tid] = (uint8_t)my_pi;
-        } else if (tid < kTileWords + kTileRows) {
-            const uint32_t r = tid - kTileWords;
+        }
+        // (a CTA with fewer threads than words + rows lets its first threads take the rows as well)
+        constexpr bool kRowThreadsApart = kExpandThreads >= kTileWords + kTileRows;
+        if (kRowThreadsApart ? (tid >= kTileWords && tid < kTileWords + kTileRows) : (tid < kTileRows)) {
+            const uint32_t r = kRowThreadsApart ? tid - kTileWords : tid;
             const uint32_t row = (uint32_t)in.perm[r];
             const u64 rq = in.req[r];
             sm.row_off[r] = (u64)row * row_stride;
