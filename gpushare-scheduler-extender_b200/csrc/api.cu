@@ -224,9 +224,9 @@ CtxLease lease_ctx(gs_snapshot* s, bool device_call) {
         l.lk = std::unique_lock<std::mutex>(l.c->mu);
         return l;
     }
-    const uint32_t start = s->ctx_rr.fetch_add(1, std::memory_order_relaxed);
-    for (int k = 0; k < gs::kFilterCtxs - 1; ++k) {
-        FilterCtx* c = &s->ctx[1 + (start + k) % (gs::kFilterCtxs - 1)];
+    // the lowest free one first: a single caller keeps using the context whose staging buffers it has already grown
+    for (int k = 1; k < gs::kFilterCtxs; ++k) {
+        FilterCtx* c = &s->ctx[k];
         std::unique_lock<std::mutex> lk(c->mu, std::try_to_lock);
         if (lk.owns_lock()) {
             l.c = c;
@@ -234,6 +234,7 @@ CtxLease lease_ctx(gs_snapshot* s, bool device_call) {
             return l;
         }
     }
+    const uint32_t start = s->ctx_rr.fetch_add(1, std::memory_order_relaxed);
     l.c = &s->ctx[1 + start % (gs::kFilterCtxs - 1)];
     l.lk = std::unique_lock<std::mutex>(l.c->mu);
     return l;
