@@ -496,6 +496,37 @@ def strong_c4(args, gsx, torch, dist, tm, rank, world, local_rank, dev, reqs, pe
             h_cut.copy_(d_cut, non_blocking=True)
         torch.cuda.current_stream(dev).synchronize()
 
+    # the gather done by the rank kernel itself: every rank's k_node_rank stores its slice into all ranks' copies of the
+    # gathered array (symmetric memory, plain peer stores over NVLink), then one device-side barrier
+    peer = None
+    try:
+        import torch.distributed._symmetric_memory as symm
+
+        bufs, ptrs, hdl = [], [], None
+        for _ in range(2):
+            t = symm.empty(world * sh.per_shard, dtype=torch.int16, device=dev)
+            hdl = symm.rendezvous(t, dist.group.WORLD)
+            t.zero_()
+            bufs.append(t)
+            ptrs.append([int(x) for x in hdl.buffer_ptrs])
+        torch.cuda.synchronize()
+        dist.barrier()
+        peer = (hdl, bufs, ptrs)
+    except Exception as ex:  # report, do not hide
+        peer_error = repr(ex)
+
+    def compact_peer(i):
+        hdl, bufs, ptrs = peer
+        snap.filter_batch_compact_device_gather(d_req.data_ptr(), P, ptrs[i & 1], rank * sh.per_shard, sh.per_shard, d_cut.data_ptr(), stream)
+        hdl.barrier(channel=0)
+
+    def compact_peer_d2h(i):
+        compact_peer(i)
+        if rank == 0:
+            h_rank.copy_(peer[1][i & 1], non_blocking=True)
+            h_cut.copy_(d_cut, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+
     K = max(5, min(args.steps, 50))
     R = max(3, min(args.repeats, 5))
     evals = P * sc.n_nodes
@@ -508,6 +539,17 @@ def strong_c4(args, gsx, torch, dist, tm, rank, world, local_rank, dev, reqs, pe
         ms = tm.loop_ms(fn, K, R, warmup=3)
         sp = _spread(ms)
         out[name] = {"ms_per_step": sp["median"], "ms_min": sp["min"], "ms_max": sp["max"], "evals_per_sec": evals / (sp["median"] * 1e-3)}
+    if peer is not None:
+        for name, fn in (("compact_peer_gather", compact_peer), ("compact_peer_gather_d2h_one_host", compact_peer_d2h)):
+            sp = _spread(tm.loop_ms(fn, K, R, warmup=4))
+            out[name] = {"ms_per_step": sp["median"], "ms_min": sp["min"], "ms_max": sp["max"], "evals_per_sec": evals / (sp["median"] * 1e-3)}
+        compact_gather(0)
+        compact_peer(0)
+        torch.cuda.synchronize()
+        out["peer_gather_equals_nccl_gather"] = bool((peer[1][0] == g_rank).all().item())
+        out["peer_gather"] = "k_node_rank stores its slice into every rank's copy (torch symmetric memory, peer stores over NVLink) + one symmetric-memory barrier"
+    else:
+        out["peer_gather_error"] = peer_error
     out["bytes_to_host_per_step"] = {"bitmap": world * P * stride * 4, "compact": world * sh.per_shard * 2 + P * 2}
     # parity spot check inside the bench run: the gathered compact form implies the gathered bitmap (first 64 pods)
     kernel_gather(0)

@@ -40,7 +40,7 @@ EXPORTS = [
     "gs_read_used", "gs_read_pods", "gs_host_alloc", "gs_host_free", "gs_profile_enable", "gs_profile_read",
     "gs_profile_reset", "gs_launch_count", "gs_device_ptrs", "gs_pods_apply_static", "gs_set_option",
     "gs_pods_apply_async", "gs_snapshot_sync", "gs_snapshot_external_write", "gs_filter_batch_subset",
-    "gs_filter_batch_compact", "gs_filter_batch_compact_device", "gs_sm_count",
+    "gs_filter_batch_compact", "gs_filter_batch_compact_device", "gs_sm_count", "gs_filter_batch_compact_device_gather",
 ]
 
 
@@ -105,6 +105,7 @@ def load():
         "gs_filter_batch_compact": (C.c_int, [vp, vp, u32, vp, u32, vp]),
         "gs_filter_batch_compact_device": (C.c_int, [vp, vp, u32, vp, u32, vp, vp]),
         "gs_sm_count": (C.c_int, [vp, C.POINTER(C.c_int)]),
+        "gs_filter_batch_compact_device_gather": (C.c_int, [vp, vp, u32, C.POINTER(vp), u32, u32, u32, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -265,6 +266,13 @@ class Snapshot:
                                     stream: int = 0):
         _check(load().gs_filter_batch_compact_device(self.h, C.c_void_p(d_req_ptr), n_pods, C.c_void_p(d_rank_ptr),
                                                      rank_stride, C.c_void_p(d_cutoff_ptr), C.c_void_p(stream)))
+
+    def filter_batch_compact_device_gather(self, d_req_ptr: int, n_pods: int, dst_ptrs, dst_offset: int, slice_count: int,
+                                           d_cutoff_ptr: int, stream: int = 0):
+        """The shard's ranks written to dst_ptrs[k] + dst_offset for every k (this GPU's and the peers' gathered arrays)."""
+        arr = (C.c_void_p * len(dst_ptrs))(*[C.c_void_p(int(p)) for p in dst_ptrs])
+        _check(load().gs_filter_batch_compact_device_gather(self.h, C.c_void_p(d_req_ptr), n_pods, arr, len(dst_ptrs), dst_offset,
+                                                            slice_count, C.c_void_p(d_cutoff_ptr), C.c_void_p(stream)))
 
     def filter_batch_device(self, d_req_ptr: int, n_pods: int, d_out_ptr: int, row_stride_words: int, stream: int = 0):
         _check(load().gs_filter_batch_device(self.h, C.c_void_p(d_req_ptr), n_pods, C.c_void_p(d_out_ptr),

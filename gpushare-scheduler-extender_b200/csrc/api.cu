@@ -392,9 +392,13 @@ int compact_device_locked(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32
         uint32_t launched = 0;
         cudaError_t le = cudaSuccess;
         int rc = timed(s, GS_K_COMPACT, st, 0, [&] {
+            gs::RankDsts dsts = {};
+            dsts.p[0] = d_rank + (size_t)k * rank_stride;
+            dsts.n = 1;
+            dsts.offset = 0;
+            dsts.count = s->n_nodes;
             le = gs::launch_compact(d_req + p0, n, c.d_cslices, c.d_csorted, c.d_cdup, s->d_used, s->d_cap, s->d_nodeinfo,
-                                    s->n_nodes, s->max_devs, d_rank + (size_t)k * rank_stride, d_cutoff + p0, s->sm_count,
-                                    st, &launched);
+                                    s->n_nodes, s->max_devs, dsts, d_cutoff + p0, s->sm_count, st, &launched);
             return le;
         });
         s->launches += launched;
@@ -821,6 +825,40 @@ int gs_filter_batch_compact_device(gs_snapshot* s, const uint64_t* d_req, uint32
     if (rc) return rc;
     l.c->outstanding = true;
     return compact_device_locked(s, *l.c, reinterpret_cast<const u64*>(d_req), n_pods, d_out_rank, rank_stride, d_out_cutoff, st);
+}
+
+int gs_filter_batch_compact_device_gather(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods, uint16_t* const* d_rank_dsts,
+                                          uint32_t n_dsts, uint32_t dst_offset, uint32_t slice_count, uint16_t* d_out_cutoff,
+                                          void* cuda_stream) {
+    if (!s || !d_req || !d_rank_dsts || !d_out_cutoff) return fail(GS_ERR_INVALID, "null argument");
+    if (n_dsts == 0 || n_dsts > (uint32_t)gs::kMaxRankDsts) return fail(GS_ERR_INVALID, "n_dsts must be 1..%d", gs::kMaxRankDsts);
+    if (n_pods == 0 || n_pods > GS_MAX_BATCH) return fail(GS_ERR_INVALID, "n_pods must be 1..GS_MAX_BATCH (ranks are relative to one chunk)");
+    ReadLock lk(s->state_mu);
+    CtxLease l = lease_ctx(s, true);
+    FilterCtx& c = *l.c;
+    int rc = use_device(s);
+    if (rc) return rc;
+    if (slice_count < s->n_nodes) return fail(GS_ERR_INVALID, "slice_count %u < node count %u", slice_count, s->n_nodes);
+    cudaStream_t st = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : s->stream;
+    rc = order_filter(s, c, st);
+    if (rc) return rc;
+    c.outstanding = true;
+    c.prev_filter = false;
+    gs::RankDsts dsts = {};
+    for (uint32_t k = 0; k < n_dsts; ++k) {
+        if (!d_rank_dsts[k]) return fail(GS_ERR_INVALID, "null destination %u", k);
+        dsts.p[k] = d_rank_dsts[k];
+    }
+    dsts.n = n_dsts;
+    dsts.offset = dst_offset;
+    dsts.count = slice_count;
+    uint32_t launched = 0;
+    rc = timed(s, GS_K_COMPACT, st, 0, [&] {
+        return gs::launch_compact(reinterpret_cast<const u64*>(d_req), n_pods, c.d_cslices, c.d_csorted, c.d_cdup, s->d_used, s->d_cap,
+                                  s->d_nodeinfo, s->n_nodes, s->max_devs, dsts, d_out_cutoff, s->sm_count, st, &launched);
+    });
+    s->launches += launched;
+    return rc;
 }
 
 int gs_filter_batch_compact(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint16_t* out_rank, uint32_t rank_stride,

@@ -129,16 +129,16 @@ k_req_place(const u64* __restrict__ req, uint32_t n_pods, uint32_t n_slices, con
 __global__ void __launch_bounds__(256)
 k_node_rank(const u64* __restrict__ sorted, uint32_t n_pods, uint32_t* __restrict__ dup, const u64* __restrict__ used,
             const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, uint32_t dev_stride,
-            uint16_t* __restrict__ rank) {
+            RankDsts dst) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     pdl_launch_dependents();
     bool eligible = false;
     const u64 key = node_key(used, cap, nodeinfo, n_nodes, dev_stride, i, &eligible);  // independent of the request side
     pdl_wait();  // the sorted requests
     if (i < n_pods) dup[i] = 0;
-    if (i >= n_nodes) return;
+    if (i >= dst.count) return;
     uint32_t lo = 0;
-    if (eligible) {
+    if (eligible) {  // (false beyond the nodes: the padding of a shard's slice is written as zero)
         uint32_t len = n_pods;
         while (len > 0) {
             const uint32_t half = len >> 1;
@@ -150,7 +150,8 @@ k_node_rank(const u64* __restrict__ sorted, uint32_t n_pods, uint32_t* __restric
             }
         }
     }
-    rank[i] = (uint16_t)lo;
+    // one destination, or this shard's slice of the gathered array on every GPU (peer stores over NVLink)
+    for (uint32_t k = 0; k < dst.n; ++k) dst.p[k][dst.offset + i] = (uint16_t)lo;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -194,7 +195,7 @@ static cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, 
 
 cudaError_t launch_compact(const u64* d_req, uint32_t n_pods, u64* d_slices, u64* d_sorted, uint32_t* d_dup,
                            const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo, uint32_t n_nodes,
-                           uint32_t dev_stride, uint16_t* d_rank, uint16_t* d_cutoff, int sm_count, cudaStream_t st,
+                           uint32_t dev_stride, const RankDsts& dsts, uint16_t* d_cutoff, int sm_count, cudaStream_t st,
                            uint32_t* n_launches) {
     *n_launches = 0;
     if (n_pods == 0 || n_pods > GS_MAX_BATCH) return cudaErrorInvalidValue;
@@ -219,9 +220,9 @@ cudaError_t launch_compact(const u64* d_req, uint32_t n_pods, u64* d_slices, u64
                    n_slices, (const u64*)d_slices, d_dup, d_sorted, d_cutoff);
     if (e != cudaSuccess) return e;
     ++*n_launches;
-    const uint32_t n_threads = n_nodes > n_pods ? n_nodes : n_pods;
+    const uint32_t n_threads = dsts.count > n_pods ? dsts.count : n_pods;
     e = launch_pdl(k_node_rank, dim3((n_threads + 255) / 256), dim3(256), 0, st, (const u64*)d_sorted,
-                   n_pods, d_dup, d_used, d_cap, d_nodeinfo, n_nodes, dev_stride, d_rank);
+                   n_pods, d_dup, d_used, d_cap, d_nodeinfo, n_nodes, dev_stride, dsts);
     if (e != cudaSuccess) return e;
     ++*n_launches;
     return cudaSuccess;

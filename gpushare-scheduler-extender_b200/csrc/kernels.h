@@ -52,11 +52,21 @@ cudaError_t launch_bind_scan(const gs_bind_req* d_binds, uint32_t n, const unsig
 cudaError_t launch_fill_i32(int32_t* d, int32_t v, size_t n, cudaStream_t st);
 
 // compact and candidate-list forms of K3 (compact_kernels.cu)
+// Where k_node_rank writes the ranks: one destination (the caller's buffer) or several -- this GPU's slice of a
+// gathered [ranks][count] array on every GPU of the box, the peers' copies reached through NVLink by plain stores
+// (the all-gather of the sharded compact Filter, done by the kernel that produces the data).
+constexpr int kMaxRankDsts = 16;
+struct RankDsts {
+    uint16_t* p[kMaxRankDsts];  // base of each destination array
+    uint32_t n;                 // destinations in use
+    uint32_t offset;            // first element written in each (this shard's slice)
+    uint32_t count;             // elements written: the nodes, then zeros up to here
+};
 // rank[n] = #{p : req[p] <= key[n]} (0 for a node that can never pass), cutoff[p] = 1 + #{q : req[q] < req[p]}:
 // pass(p, n) <=> rank[n] >= cutoff[p].  Three launches; returns how many were made through *n_launches.
 cudaError_t launch_compact(const unsigned long long* d_req, uint32_t n_pods, unsigned long long* d_slices, unsigned long long* d_sorted,
                            uint32_t* d_dup, const unsigned long long* d_used, const unsigned long long* d_cap,
-                           const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint16_t* d_rank,
+                           const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, const RankDsts& dsts,
                            uint16_t* d_cutoff, int sm_count, cudaStream_t st, uint32_t* n_launches);
 // bit c of row p = predicate(pod p, node subset[c]); one launch
 cudaError_t launch_filter_subset(const unsigned long long* d_req, uint32_t n_pods, const uint32_t* d_subset, uint32_t n_cand,

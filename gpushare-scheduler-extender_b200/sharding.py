@@ -87,6 +87,7 @@ class ShardedCluster:
         self.sh, self.rank, self.engine, self.dist, self.device = sharding, rank, engine, dist, device
         self._gathered = None
         self._gathered_rank = None
+        self._peer = None  # (symmetric-memory handle, [two gathered rank buffers], their peer pointers, step counter)
 
     # ---- small host arrays from rank 0 to everybody (requests, binds, events), as one device tensor ----
     def _bcast_array(self, arr_on_rank0, dtype: np.dtype) -> np.ndarray:
@@ -141,6 +142,28 @@ class ShardedCluster:
         g = self.filter_device(self.broadcast_requests(req_on_rank0))
         return self.sh.assemble_bitmap(g.cpu().numpy().view(np.uint32))
 
+    def enable_peer_gather(self):
+        """Let the rank kernel itself do the all-gather of the compact Filter: the gathered [G][per_shard] array lives in
+        symmetric memory (every GPU's copy mapped into every process over NVLink) and each rank's kernel stores its
+        slice into all G copies; one device-side barrier per call replaces the NCCL collective.  Two buffers alternate,
+        so a rank that is one call ahead never writes what a peer may still be reading.  NCCL ranks on CUDA only."""
+        import torch
+        import torch.distributed._symmetric_memory as symm
+
+        n = self.sh.world * self.sh.per_shard
+        bufs, ptrs = [], []
+        hdl = None
+        for _ in range(2):
+            t = symm.empty(n, dtype=torch.int16, device=self.device)
+            h = symm.rendezvous(t, self.dist.group.WORLD)
+            t.zero_()
+            bufs.append(t)
+            ptrs.append([int(p) for p in h.buffer_ptrs])
+            hdl = h
+        torch.cuda.synchronize()
+        self.dist.barrier()
+        self._peer = [hdl, bufs, ptrs, 0]
+
     def filter_compact_device(self, req):
         """Returns (rank [G][per_shard] int16 tensor, cutoff [P] int16 tensor) on `device`:
         pass(p, n) <=> rank[n // per_shard, n % per_shard] >= cutoff[p] (as unsigned 16-bit values).  Ranks are
@@ -148,6 +171,13 @@ class ShardedCluster:
         the ranks are gathered."""
         import torch
 
+        if self._peer is not None:
+            hdl, bufs, ptrs, step = self._peer
+            k = step & 1
+            self._peer[3] = step + 1
+            cutoff = self.engine.filter_compact_gather(req, ptrs[k], self.rank * self.sh.per_shard, self.sh.per_shard)
+            hdl.barrier(channel=0)  # every rank's slice has landed in every copy
+            return bufs[k].view(self.sh.world, self.sh.per_shard), cutoff
         rank_local, cutoff = self.engine.filter_compact(req, self.sh.per_shard)
         if self.dist is None:
             return rank_local[None], cutoff
@@ -219,13 +249,25 @@ class SnapshotEngine:
 
         P = int(req.numel())
         assert P <= MAX_BATCH, "one chunk of ranks per call"
-        if self._rank is None or self._rank.numel() != rank_stride or self._cutoff.numel() != P:
+        if self._rank is None or self._rank.numel() != rank_stride or self._cutoff is None or self._cutoff.numel() != P:
             self._rank = torch.zeros(rank_stride, dtype=torch.int16, device=req.device)
             self._cutoff = torch.zeros(P, dtype=torch.int16, device=req.device)
         if P:
             self.snap.filter_batch_compact_device(req.data_ptr(), P, self._rank.data_ptr(), rank_stride, self._cutoff.data_ptr(),
                                                   _current_stream_handle(req.device))
         return self._rank, self._cutoff
+
+    def filter_compact_gather(self, req, dst_ptrs, dst_offset, slice_count):
+        """The shard's ranks stored by the kernel into every array of dst_ptrs (this GPU's and the peers'); returns the
+        cutoffs (the same on every rank)."""
+        import torch
+
+        P = int(req.numel())
+        if self._cutoff is None or self._cutoff.numel() != P:
+            self._cutoff = torch.zeros(P, dtype=torch.int16, device=req.device)
+        self.snap.filter_batch_compact_device_gather(req.data_ptr(), P, dst_ptrs, dst_offset, slice_count, self._cutoff.data_ptr(),
+                                                     _current_stream_handle(req.device))
+        return self._cutoff
 
     def bind(self, binds):
         return self.snap.bind_batch(binds)

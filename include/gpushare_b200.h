@@ -209,6 +209,16 @@ int gs_filter_batch_compact(gs_snapshot* s, const uint64_t* req, uint32_t n_pods
 /* Same with device buffers, asynchronous on `cuda_stream` (padding of d_out_rank is left untouched). */
 int gs_filter_batch_compact_device(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods, uint16_t* d_out_rank,
                                    uint32_t rank_stride, uint16_t* d_out_cutoff, void* cuda_stream);
+/* The compact Filter of one node shard, gathered by the kernel that computes it: the shard's ranks go to
+ * d_rank_dsts[k][dst_offset .. dst_offset + slice_count) for every k < n_dsts (<= 16) -- the nodes' ranks first, zeros up
+ * to slice_count.  The destinations are device addresses valid in this process: this GPU's copy of the gathered
+ * [shards][slice_count] array and the peers' copies mapped over NVLink (e.g. the buffer_ptrs of a torch symmetric-memory
+ * allocation); the kernel reaches them with plain stores.  One chunk only (n_pods <= GS_MAX_BATCH).  The caller orders
+ * the GPUs against each other afterwards (a barrier over the same peers) before any of them reads the gathered array.
+ * SURVEY.md 8e's "NVLink gather of ... binpack winners" in its compact form; no counterpart in the reference. */
+int gs_filter_batch_compact_device_gather(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods, uint16_t* const* d_rank_dsts,
+                                          uint32_t n_dsts, uint32_t dst_offset, uint32_t slice_count, uint16_t* d_out_cutoff,
+                                          void* cuda_stream);
 /* Profiling aid: launches only the K3 stages named in stage_mask (GS_STAGE_*), in order, on the
  * same buffers gs_filter_batch_device uses (n_pods <= GS_MAX_BATCH).  Later stages read what earlier
  * stages left in the snapshot's work buffers, so run the full set once first.  bench.py times each

@@ -136,8 +136,15 @@ def _nccl_worker(rank, world, port, out_dir):
         cl.apply_events(ev if rank == 0 else None)
         g2 = cl.filter_device(req_t).cpu().numpy().view(np.uint32).copy()
         rk, cut = cl.filter_compact_device(req_t)
-        np.savez(os.path.join(out_dir, f"r{rank}.npz"), g0=g0, devs=devs, g1=g1, g2=g2,
-                 rk=rk.cpu().numpy().view(np.uint16), cut=cut.cpu().numpy().view(np.uint16))
+        rk, cut = rk.cpu().numpy().view(np.uint16).copy(), cut.cpu().numpy().view(np.uint16).copy()
+        # the same with the gather done by the rank kernel itself (peer stores into symmetric memory), several calls
+        # in a row so that both of its alternating buffers are used and reused
+        cl.enable_peer_gather()
+        peer_ok = True
+        for _ in range(5):
+            rk2, cut2 = cl.filter_compact_device(req_t)
+            peer_ok &= bool((rk2.cpu().numpy().view(np.uint16) == rk).all() and (cut2.cpu().numpy().view(np.uint16) == cut).all())
+        np.savez(os.path.join(out_dir, f"r{rank}.npz"), g0=g0, devs=devs, g1=g1, g2=g2, rk=rk, cut=cut, peer_ok=np.array(peer_ok))
         snap.close()
     finally:
         dist.destroy_process_group()
@@ -170,3 +177,4 @@ def test_two_nccl_ranks_match_unsharded(tmp_path):
     assert (sh.assemble_bitmap(r0["g2"]) == _globalise(sh, p2)).all()
     rank = sh.assemble_rank(r0["rk"])
     assert (rank == rank_want).all() and ((rank[None, :] >= r0["cut"][:, None]) == p2).all()
+    assert all(bool(r["peer_ok"]) for r in res), "the kernel-side gather over peer memory differs from the NCCL gather"
