@@ -150,3 +150,34 @@ def test_subset_at_c4_scale():
             got = s.filter_batch_subset(reqs, sub)
             want = (key[sub][None, :] >= reqs[:, None]) & elig[sub][None, :]
             assert (got == S.pack_bitmap(want, got.shape[1])).all()
+
+
+def test_compact_gather_entry_point_writes_every_destination():
+    """gs_filter_batch_compact_device_gather on one GPU: two destination arrays stand in for "this GPU's copy and a peer's
+    copy" of the gathered [shards][slice] array; the shard's ranks must land at the given offset of both, zero padded
+    to the slice length, and nothing else may be touched."""
+    import torch
+
+    sc = synth.make_cluster(1000, 8, 184320, running=6000, seed=6, quirks=True, fill=0.9)
+    cap, used, ndev, cls, _ = H.soa_state(sc)
+    key, elig = S.node_keys(cap, used, ndev, cls)
+    P, slice_len, offset = 3000, 1024, 1024                      # shard 1 of 3
+    reqs = hard_requests(P, np.random.default_rng(6))
+    with H.load_snapshot(sc) as s:
+        d_req = torch.from_numpy(reqs.view(np.int64)).cuda()
+        dsts = [torch.full((3 * slice_len,), -1, dtype=torch.int16, device="cuda") for _ in range(2)]
+        d_cut = torch.zeros(P, dtype=torch.int16, device="cuda")
+        st = torch.cuda.Stream()
+        torch.cuda.synchronize()
+        s.filter_batch_compact_device_gather(d_req.data_ptr(), P, [d.data_ptr() for d in dsts], offset, slice_len,
+                                             d_cut.data_ptr(), st.cuda_stream)
+        st.synchronize()
+        srt = np.sort(reqs)
+        want = np.full(3 * slice_len, 0xFFFF, np.uint16)
+        want[offset: offset + slice_len] = 0
+        want[offset: offset + sc.n_nodes] = np.where(elig, np.searchsorted(srt, key, side="right"), 0)
+        for d in dsts:
+            assert (d.cpu().numpy().view(np.uint16) == want).all()
+        assert (d_cut.cpu().numpy().view(np.uint16) == 1 + np.searchsorted(srt, reqs, side="left")).all()
+        with pytest.raises(gsx.GpushareError):
+            s.filter_batch_compact_device_gather(d_req.data_ptr(), P, [dsts[0].data_ptr()], 0, sc.n_nodes - 1, d_cut.data_ptr(), 0)

@@ -1,3 +1,8 @@
+// NOT PART OF THE BUILD.  An experiment of round 2, kept for the record with its measurements in profiles/NOTES.md 21-23: it was
+// included from filter_kernels.cu after k_expand and needs what was removed with it -- `planes_low` / `shift` in FilterBuffers
+// (bit planes of the key bits below the bucket scale, written by k_prep's node role), kLowPlanes = 10, 256 + 256 words of
+// per-group scheduler state per buffer set, and an expand epoch that counts finished warps (commit dc86a05 has all of it).
+//
 // k_expand_warp: the bitmap writer of K3, one warp per tile, registers only.
 //
 // A warp tile is kWarpRows consecutive grouped pods x kTileWords words (4096 nodes).  The warp loads what the tile
