@@ -522,6 +522,8 @@ struct ExpandSmem {
     uint32_t stage[kStageWords];
     u64 req[kTileRows];                 // requests of the tile's rows (~0 beyond the last row)
     u64 req_sorted[kTileRows];          // the same in ascending order (dense tiles)
+    __align__(16) uint32_t req_sorted32[kTileRows];  // ... saturated to 32 bits (exact in a tile that is not "wide")
+    __align__(16) uint32_t pivot[kTileRows / 4];     // req_sorted32[3], [7], [11], ...: the search's upper levels
     u64 off_sorted[kTileRows];
     u64 row_off[kTileRows];             // word offset of every tile row's output row (pod index x row stride)
     uint32_t basew[kTileWords];         // nodes passing in every row
@@ -585,7 +587,7 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 
 #ifdef GS_EXPAND_TRACE
 // development builds only: per CTA and tile, SM cycle stamps of the phases (tools/expand_trace.py)
-constexpr int kTraceTiles = 6, kTraceSlots = 12;
+constexpr int kTraceTiles = 6, kTraceSlots = 16;
 __device__ unsigned long long g_trace[148 * 5 * kTraceTiles * kTraceSlots];
 #define GS_TRACE(slot) \
     do { if (tid == 0 && it < kTraceTiles) g_trace[((size_t)blockIdx.x * kTraceTiles + it) * kTraceSlots + (slot)] = clock64(); } while (0)
@@ -747,16 +749,29 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
 
         // Dense tiles want the tile's rows in ascending request order: then a node's column is a prefix of
         // ones and one binary search per node replaces a comparison per row.
-        if (dense && tid < kTileRows) {
-            const u64 mine = sm.req[tid];
+        // (rank by counting; the kSortParts lanes of a row each count a share of the other rows)
+        constexpr uint32_t kSortParts = kExpandThreads / kTileRows >= 4 ? 4u : 1u;
+        if (dense && tid < kTileRows * kSortParts) {
+            const uint32_t r = tid / kSortParts, part = tid % kSortParts;
+            const u64 mine = sm.req[r];
             uint32_t rank = 0;
-#pragma unroll 8
-            for (uint32_t o = 0; o < kTileRows; ++o) {
+#pragma unroll
+            for (uint32_t i = 0; i < kTileRows / kSortParts; ++i) {
+                const uint32_t o = part * (kTileRows / kSortParts) + i;
                 const u64 other = sm.req[o];
-                rank += (other < mine || (other == mine && o < tid)) ? 1u : 0u;
+                rank += (other < mine || (other == mine && o < r)) ? 1u : 0u;
             }
-            sm.req_sorted[rank] = mine;
-            sm.off_sorted[rank] = sm.row_off[tid];
+            if (kSortParts == 4) {
+                rank += __shfl_xor_sync(0xffffffffu, rank, 1);
+                rank += __shfl_xor_sync(0xffffffffu, rank, 2);
+            }
+            if (part == 0) {
+                sm.req_sorted[rank] = mine;
+                const uint32_t mine32 = (mine >> 32) != 0 ? 0xffffffffu : (uint32_t)mine;
+                sm.req_sorted32[rank] = mine32;
+                if ((rank & 3u) == 3u) sm.pivot[rank >> 2] = mine32;
+                sm.off_sorted[rank] = sm.row_off[r];
+            }
         }
         GS_TRACE(3);
 
@@ -813,9 +828,54 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     mbar_wait(&key_bar, key_phase, fb.fault, kFaultTileKeys);
                     key_phase ^= 1u;
                     GS_TRACE(11);
-                    // each warp owns partial words warp, warp + 8, ... and runs four of them at a time, so
-                    // that four independent binary searches hide each other's shared-memory latency
-                    for (uint32_t k0 = warp; k0 < np; k0 += 4 * kWarps) {
+                    // Each warp owns partial words warp, warp + 8, ... and runs several of them at a time, so that
+                    // their independent searches share each round trip to shared memory (on an SM that is streaming
+                    // stores a dependent shared-memory access costs the better part of a thousand cycles).  With
+                    // 32-bit operands: eight words at a time, the 64 sorted requests searched as 4 blocks of 4
+                    // groups of 4 -- one comparison round against the block ends (registers), one against the
+                    // chosen block's group ends and one against the chosen group: two 16-byte loads per word
+                    // instead of six dependent ones.
+                    if (!wide) {
+                        constexpr int kWay = 8;
+                        static_assert(kTileRows == 64, "three levels of four");
+                        const uint4 ends = make_uint4(sm.pivot[3], sm.pivot[7], sm.pivot[11], 0u);  // (the last block has no end to test)
+                        for (uint32_t k0 = warp; k0 < np; k0 += kWay * kWarps) {
+                            uint32_t cnt[kWay], key[kWay];
+#pragma unroll
+                            for (int u = 0; u < kWay; ++u) {
+                                const uint32_t k = k0 + u * kWarps;
+                                key[u] = k < np ? sm.stage[(uint32_t)sm.plist[k] * 32 + lane] : 0u;
+                                cnt[u] = 16u * ((ends.x <= key[u]) + (ends.y <= key[u]) + (ends.z <= key[u]));  // 0..48
+                            }
+#pragma unroll
+                            for (int u = 0; u < kWay; ++u) {
+                                const uint4 gq = *reinterpret_cast<const uint4*>(&sm.pivot[cnt[u] >> 2]);
+                                cnt[u] += 4u * ((gq.x <= key[u]) + (gq.y <= key[u]) + (gq.z <= key[u]));
+                            }
+#pragma unroll
+                            for (int u = 0; u < kWay; ++u) {
+                                const uint4 e = *reinterpret_cast<const uint4*>(&sm.req_sorted32[cnt[u]]);
+                                cnt[u] += (e.x <= key[u]) + (e.y <= key[u]) + (e.z <= key[u]) + (e.w <= key[u]);
+                            }
+#pragma unroll
+                            for (int u = 0; u < kWay; ++u) {
+                                const uint32_t k = k0 + u * kWarps;
+                                if (k >= np) continue;  // warp-uniform
+                                const uint32_t t = sm.plist[k];
+                                uint32_t c = min(cnt[u], rows);  // a saturated key also matches the padding rows
+                                if (!((sm.somew[t] >> lane) & 1u)) c = 0;  // (see below)
+                                uint32_t mine = 0;
+#pragma unroll
+                                for (int q = 0; q < kDensePlanes; ++q) {
+                                    const uint32_t bal = __ballot_sync(0xffffffffu, (c >> q) & 1u);
+                                    if ((int)lane == q) mine = bal;
+                                }
+                                if (lane < kDensePlanes) sm.cntp[lane * kTileWords + t] = mine;
+                            }
+                        }
+                    }
+                    // ... with the 64-bit operands of a wide tile: four at a time, plain binary search
+                    for (uint32_t k0 = warp; wide && k0 < np; k0 += 4 * kWarps) {
                         uint32_t cnt[4], t[4];
                         u64 key[4];
                         bool on[4];
@@ -852,10 +912,14 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                             if (lane < kDensePlanes) sm.cntp[lane * kTileWords + t[u]] = mine;
                         }
                     }
+                    GS_TRACE(12);
+                    // the ticket of a dense tile is taken late (see the schedule note above): when this warp's
+                    // share of the last pass is done, so that the round trip overlaps the wait for the other warps
+                    if (tid == 0 && pass + 1 == passes) ticket = atomicAdd(&fb.sched[0], 1u);
                     __syncthreads();  // counts complete; the key area may be overwritten
+                    GS_TRACE(13);
                 }
-                if (tid == 0) {  // the ticket of a dense tile is taken late: see the schedule note above
-                    ticket = atomicAdd(&fb.sched[0], 1u);
+                if (tid == 0) {
                     sm.next_tile = gridDim.x + ticket;
                     request(sm.next_tile, stage ^ 1u);
                 }
@@ -902,13 +966,31 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     uint32_t* dst = out + wcol;
                     const uint32_t k0 = p4 & 0xffu, k1 = (p4 >> 8) & 0xffu, k2 = (p4 >> 16) & 0xffu, k3 = p4 >> 24;
                     if (dense) {
+                        // The lane's count planes do not depend on the row: loaded once, ahead of every store.  Its
+                        // rows are row_step (a multiple of 8) apart, so the three low bits of row + 1 are the same
+                        // for all of them and the three low planes fold into one value up front.
+                        static_assert(kWarps % 8 == 0 && kDensePlanes > 3, "low bits of the lane's rows are fixed");
+                        uint4 low = make_uint4(~0u, ~0u, ~0u, ~0u);
+#pragma unroll
+                        for (int q = 0; q < 3; ++q) {
+                            const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lcol * 4]);
+                            if (((row0 + 1u) >> q) & 1u) {
+                                low.x &= pl.x; low.y &= pl.y; low.z &= pl.z; low.w &= pl.w;
+                            } else {
+                                low.x |= pl.x; low.y |= pl.y; low.z |= pl.z; low.w |= pl.w;
+                            }
+                        }
+                        uint4 cp[kDensePlanes - 3];
+#pragma unroll
+                        for (int q = 3; q < kDensePlanes; ++q)
+                            cp[q - 3] = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lcol * 4]);
                         for (uint32_t rr = row0; rr < rows; rr += row_step) {
                             // bit set iff the node's pass count reaches (sorted) row + 1
                             const uint32_t thr = rr + 1;
-                            uint4 ge = make_uint4(~0u, ~0u, ~0u, ~0u);
+                            uint4 ge = low;
 #pragma unroll
-                            for (int q = 0; q < kDensePlanes; ++q) {
-                                const uint4 pl = *reinterpret_cast<const uint4*>(&sm.cntp[q * kTileWords + lcol * 4]);
+                            for (int q = 3; q < kDensePlanes; ++q) {
+                                const uint4 pl = cp[q - 3];
                                 if ((thr >> q) & 1u) {
                                     ge.x &= pl.x; ge.y &= pl.y; ge.z &= pl.z; ge.w &= pl.w;
                                 } else {

@@ -37,3 +37,35 @@ f = lambda v: f"{(int(v) - t0) / 1e3:7.1f}"
 print("launch | prep: entry first..last, [atomic back first..last, counts complete first..last], past-wait last, exit last | expand: entry first..last, past-wait first..last, exit first..last")
 for q in order[4:16]:
     print(f"{q:4d}   | {f(lo[q,0,0])}..{f(hi[q,0,0])} [{f(lo[q,0,3])}..{f(hi[q,0,3])} {f(lo[q,0,4])}..{f(hi[q,0,4])}] {f(hi[q,0,1])} {f(hi[q,0,2])} | {f(lo[q,1,0])}..{f(hi[q,1,0])}  {f(lo[q,1,1])}..{f(hi[q,1,1])}  {f(lo[q,1,2])}..{f(hi[q,1,2])}")
+
+# per-tile phase stamps of the LAST launch (SM cycles, thread 0 of each CTA): medians over the CTAs' clean tiles
+kT, kS = 6, 16
+tr = np.zeros(148 * 5 * kT * kS, dtype=np.uint64)
+assert lib.gs_debug_expand_trace(tr.ctypes.data_as(C.POINTER(C.c_uint64)), tr.size) == 0
+tr = tr.reshape(148 * 5, kT, kS).astype(np.int64)
+names = ["wait inputs 0-1", "phase A 1-2", "keys/ticket 2-3", "stores issued 3-6", "end sync 6-7", "to next tile 7-0'"]
+for it in range(4):
+    ok = (tr[:, it, 7] > tr[:, it, 0]) & (tr[:, it, 0] > 0) & ((tr[:, it, 8] & 0xffff) == 0)
+    if ok.sum() < 10:
+        continue
+    t = tr[ok, it]
+    d = [t[:, 1] - t[:, 0], t[:, 2] - t[:, 1], t[:, 3] - t[:, 2], t[:, 6] - t[:, 3], t[:, 7] - t[:, 6]]
+    nxt = tr[ok, it + 1, 0] - t[:, 7]
+    nxt_ok = tr[ok, it + 1, 7] > tr[ok, it + 1, 0]
+    print(f"tile #{it} of a CTA, {int(ok.sum())} clean tiles: " + ", ".join(f"{n} {int(np.median(x))}" for n, x in zip(names, d)) +
+          f", {names[5]} {int(np.median(nxt[nxt_ok])) if nxt_ok.any() else -1}; whole {int(np.median(t[:, 7] - t[:, 0]))} cycles")
+
+# dense tiles of the last launch (thread 0's stamps)
+dn = ["inputs 0-1", "phase A 1-2", "sort rows 2-3", "clean lanes' stores 3-4", "barrier 4-10", "keys land 10-11",
+      "searches (warp 0) 11-12", "other warps 12-13", "ticket, request 13-5", "partial lanes' stores 5-6", "end 6-7"]
+sl = [(0, 1), (1, 2), (2, 3), (3, 4), (4, 10), (10, 11), (11, 12), (12, 13), (13, 5), (5, 6), (6, 7)]
+rows = []
+for it in range(kT):
+    ok = (tr[:, it, 7] > tr[:, it, 0]) & (tr[:, it, 0] > 0) & (((tr[:, it, 8] >> 16) & 1) == 1)
+    if ok.any():
+        rows.append(tr[ok, it])
+if rows:
+    t = np.concatenate(rows)
+    print(f"{len(t)} dense tiles, partial words median {int(np.median(t[:, 8] & 0xffff))}: " +
+          ", ".join(f"{n} {int(np.median(t[:, b] - t[:, a]))}" for n, (a, b) in zip(dn, sl)) +
+          f"; whole {int(np.median(t[:, 7] - t[:, 0]))} cycles (max {int((t[:, 7] - t[:, 0]).max())})")
