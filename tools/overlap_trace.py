@@ -69,3 +69,17 @@ if rows:
     print(f"{len(t)} dense tiles, partial words median {int(np.median(t[:, 8] & 0xffff))}: " +
           ", ".join(f"{n} {int(np.median(t[:, b] - t[:, a]))}" for n, (a, b) in zip(dn, sl)) +
           f"; whole {int(np.median(t[:, 7] - t[:, 0]))} cycles (max {int((t[:, 7] - t[:, 0]).max())})")
+
+# sparse tiles of the last launch
+sn = ["inputs 0-1", "phase A 1-2", "keys requested, ticket 2-3", "clean lanes' stores 3-4", "compares 4-5", "partial lanes' stores 5-6", "end 6-7"]
+ss = [(0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6), (6, 7)]
+rows = []
+for it in range(kT):
+    ok = (tr[:, it, 7] > tr[:, it, 0]) & (tr[:, it, 0] > 0) & (((tr[:, it, 8] >> 16) & 1) == 0) & ((tr[:, it, 8] & 0xffff) != 0)
+    if ok.any():
+        rows.append(tr[ok, it])
+if rows:
+    t = np.concatenate(rows)
+    print(f"{len(t)} sparse tiles, partial words median {int(np.median(t[:, 8] & 0xffff))}: " +
+          ", ".join(f"{n} {int(np.median(t[:, b] - t[:, a]))}" for n, (a, b) in zip(sn, ss)) +
+          f"; whole {int(np.median(t[:, 7] - t[:, 0]))} cycles (max {int((t[:, 7] - t[:, 0]).max())})")
