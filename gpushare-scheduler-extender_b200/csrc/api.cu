@@ -10,6 +10,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -111,7 +113,33 @@ int grow_pinned(gs_snapshot* s, void** p, size_t* have, size_t bytes) {
     return GS_OK;
 }
 
+// Blocks handed out by gs_host_alloc: known to be page-locked and (unified addressing) addressable by kernels under the
+// same pointer, without asking the driver on every call.
+std::mutex g_host_mu;
+std::map<uintptr_t, size_t> g_host_blocks;  // start -> bytes
+bool in_host_block(const void* p) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    auto it = g_host_blocks.upper_bound(a);
+    if (it == g_host_blocks.begin()) return false;
+    --it;
+    return a < it->first + it->second;
+}
+
+// Page-locked host memory that kernels of this device can address (cudaHostAlloc / cudaHostRegister under unified
+// addressing): the pointer kernels should use, or nullptr.
+void* device_view_of_host(const void* p) {
+    if (in_host_block(p)) return const_cast<void*>(p);
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
 bool is_pinned(const void* p) {
+    if (in_host_block(p)) return true;
     cudaPointerAttributes a;
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
         cudaGetLastError();
@@ -274,6 +302,8 @@ int alloc_ctx(gs_snapshot* s, FilterCtx& c) {
     CU(cudaMalloc(&c.d_cslices, (B + 1024) * sizeof(u64)));
     CU(cudaMalloc(&c.d_csorted, B * sizeof(u64)));
     CU(cudaMalloc(&c.d_cdup, B * sizeof(uint32_t)));
+    CU(cudaMalloc(&c.d_creq, B * sizeof(u64)));
+    CU(cudaMalloc(&c.d_ccut, B * sizeof(uint16_t)));
     CU(cudaMemsetAsync(c.d_pod_hist, 0, 2 * 512 * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_sched, 0, 4 * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_epochs, 0, 6 * sizeof(uint32_t), s->stream));
@@ -295,6 +325,8 @@ void free_ctx(FilterCtx& c) {
     cudaFree(c.d_cslices);
     cudaFree(c.d_csorted);
     cudaFree(c.d_cdup);
+    cudaFree(c.d_creq);
+    cudaFree(c.d_ccut);
     cudaFree(c.d_stage);
     cudaFree(c.d_bitmap);
     if (c.h_stage) cudaFreeHost(c.h_stage);
@@ -383,8 +415,9 @@ uint32_t expand_words_out(uint32_t words, uint32_t row_stride, const void* d_out
     return w;
 }
 
+// host_side: d_req, d_rank and d_cutoff are the device's view of page-locked host memory
 int compact_device_locked(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods, uint16_t* d_rank,
-                          uint32_t rank_stride, uint16_t* d_cutoff, cudaStream_t st) {
+                          uint32_t rank_stride, uint16_t* d_cutoff, cudaStream_t st, bool host_side = false) {
     if (rank_stride < s->n_nodes) return fail(GS_ERR_INVALID, "rank_stride %u < node count %u", rank_stride, s->n_nodes);
     c.prev_filter = false;  // (a snapshot without nodes still answers: the cutoffs depend on the requests only)
     for (uint32_t p0 = 0, k = 0; p0 < n_pods; p0 += GS_MAX_BATCH, ++k) {
@@ -398,7 +431,8 @@ int compact_device_locked(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32
             dsts.offset = 0;
             dsts.count = s->n_nodes;
             le = gs::launch_compact(d_req + p0, n, c.d_cslices, c.d_csorted, c.d_cdup, s->d_used, s->d_cap, s->d_nodeinfo,
-                                    s->n_nodes, s->max_devs, dsts, d_cutoff + p0, s->sm_count, st, &launched);
+                                    s->n_nodes, s->max_devs, dsts, d_cutoff + p0, s->sm_count, st, &launched,
+                                    host_side ? c.d_creq : nullptr, host_side ? c.d_ccut : nullptr);
             return le;
         });
         s->launches += launched;
@@ -824,7 +858,10 @@ int gs_filter_batch_compact_device(gs_snapshot* s, const uint64_t* d_req, uint32
     rc = order_filter(s, *l.c, st);
     if (rc) return rc;
     l.c->outstanding = true;
-    return compact_device_locked(s, *l.c, reinterpret_cast<const u64*>(d_req), n_pods, d_out_rank, rank_stride, d_out_cutoff, st);
+    // (buffers from gs_host_alloc are "device" buffers too: the kernels then touch host memory as little as they can)
+    const bool host_side = in_host_block(d_req) && in_host_block(d_out_cutoff);
+    return compact_device_locked(s, *l.c, reinterpret_cast<const u64*>(d_req), n_pods, d_out_rank, rank_stride, d_out_cutoff, st,
+                                 host_side);
 }
 
 int gs_filter_batch_compact_device_gather(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods, uint16_t* const* d_rank_dsts,
@@ -872,6 +909,23 @@ int gs_filter_batch_compact(gs_snapshot* s, const uint64_t* req, uint32_t n_pods
     if (n_pods == 0) return GS_OK;
     if (rank_stride < s->n_nodes) return fail(GS_ERR_INVALID, "rank_stride %u < node count %u", rank_stride, s->n_nodes);
     const uint32_t n_chunks = (n_pods + GS_MAX_BATCH - 1) / GS_MAX_BATCH;
+    // Page-locked caller buffers: the kernels read the requests and write rank[] / cutoff[] in place, over PCIe -- 80 KB
+    // in and 120 KB out at config C4's size, less than what three copies cost to set up.  The call still ends
+    // synchronised: the results are in the caller's memory when it returns.
+    if (rank_stride == s->n_nodes && s->n_nodes != 0) {
+        const u64* v_req = static_cast<const u64*>(device_view_of_host(req));
+        uint16_t* v_rank = static_cast<uint16_t*>(device_view_of_host(out_rank));
+        uint16_t* v_cut = static_cast<uint16_t*>(device_view_of_host(out_cutoff));
+        if (v_req && v_rank && v_cut) {
+            rc = order_filter(s, c, c.stream);
+            if (rc) return rc;
+            c.outstanding = true;
+            rc = compact_device_locked(s, c, v_req, n_pods, v_rank, rank_stride, v_cut, c.stream, true);
+            if (rc) return rc;
+            CU(cudaStreamSynchronize(c.stream));
+            return GS_OK;
+        }
+    }
     const size_t req_bytes = ((size_t)n_pods * sizeof(u64) + 255) & ~(size_t)255;
     const size_t rank_bytes = (size_t)n_chunks * rank_stride * sizeof(uint16_t);
     const size_t rank_pad = (rank_bytes + 255) & ~(size_t)255;
@@ -1027,11 +1081,19 @@ int gs_host_alloc(size_t bytes, void** out) {
     if (!out) return fail(GS_ERR_INVALID, "null out");
     *out = nullptr;
     CU(cudaMallocHost(out, bytes ? bytes : 1));
+    {
+        std::lock_guard<std::mutex> lk(g_host_mu);
+        g_host_blocks[reinterpret_cast<uintptr_t>(*out)] = bytes ? bytes : 1;
+    }
     return GS_OK;
 }
 int gs_host_free(void* p) {
     const gs_snapshot* s = nullptr;
     if (!p) return GS_OK;
+    {
+        std::lock_guard<std::mutex> lk(g_host_mu);
+        g_host_blocks.erase(reinterpret_cast<uintptr_t>(p));
+    }
     CU(cudaFreeHost(p));
     return GS_OK;
 }

@@ -102,6 +102,8 @@ struct FilterCtx {
     unsigned long long* d_cslices = nullptr;    // [GS_MAX_BATCH rounded up to whole slices of 1024]
     unsigned long long* d_csorted = nullptr;    // [GS_MAX_BATCH]
     uint32_t* d_cdup = nullptr;                 // [GS_MAX_BATCH] zero between calls (self re-arming)
+    unsigned long long* d_creq = nullptr;       // [GS_MAX_BATCH] device copy of requests that live in host memory
+    uint16_t* d_ccut = nullptr;                 // [GS_MAX_BATCH] cutoffs on their way to host memory
 
     void* d_stage = nullptr;   // device staging of host-buffer calls (requests, candidate lists, compact results)
     size_t d_stage_bytes = 0;

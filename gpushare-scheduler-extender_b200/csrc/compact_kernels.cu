@@ -32,12 +32,14 @@ constexpr uint32_t kMaxSlices = (GS_MAX_BATCH + kSlice - 1) / kSlice;
 // one element per thread; exchanges at distances below 32 are shuffles, the fifteen at 32 and above go through
 // shared memory
 __global__ void __launch_bounds__(kSlice)
-k_slice_sort(const u64* __restrict__ req, uint32_t n_pods, u64* __restrict__ slices) {
+k_slice_sort(const u64* __restrict__ req, uint32_t n_pods, u64* __restrict__ slices, u64* __restrict__ req_copy) {
     __shared__ u64 v[kSlice];
     const uint32_t tid = threadIdx.x;
     const uint32_t base = blockIdx.x * kSlice;
     pdl_launch_dependents();
     u64 mine = base + tid < n_pods ? req[base + tid] : ~0ull;
+    // requests that live in host memory are read over PCIe once: the next kernel takes them from this copy
+    if (req_copy && base + tid < n_pods) req_copy[base + tid] = mine;
     for (uint32_t k = 2; k <= kSlice; k <<= 1) {
         const bool asc = (tid & k) == 0;
         for (uint32_t j = k >> 1; j > 0; j >>= 1) {
@@ -65,14 +67,17 @@ k_slice_sort(const u64* __restrict__ req, uint32_t n_pods, u64* __restrict__ sli
 // lt and distinct requests distinct lt, so the duplicate counter of a value lives at dup[lt]; the lanes of a warp
 // that share a value go to it as one atomic.
 __global__ void __launch_bounds__(64)
-k_req_place(const u64* __restrict__ req, uint32_t n_pods, uint32_t n_slices, const u64* __restrict__ g_slices,
-            uint32_t* __restrict__ dup, u64* __restrict__ sorted, uint16_t* __restrict__ cutoff) {
+k_req_place(const u64* __restrict__ req_early, const u64* __restrict__ req_late, uint32_t n_pods, uint32_t n_slices,
+            const u64* __restrict__ g_slices, uint32_t* __restrict__ dup, u64* __restrict__ sorted,
+            uint16_t* __restrict__ cutoff) {
     extern __shared__ __align__(16) u64 slices[];  // every block keeps all the slices at hand: the searches are dependent loads
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31;
     pdl_launch_dependents();
-    const u64 mine = p < n_pods ? req[p] : 0ull;
+    // the request: from the caller's device array before the wait, or after it from the copy k_slice_sort made
+    u64 mine = (req_early && p < n_pods) ? req_early[p] : 0ull;
     pdl_wait();  // the sorted slices
+    if (!req_early && p < n_pods) mine = req_late[p];
     {
         // one bulk asynchronous copy (TMA) per slice, all in flight together, completion on an mbarrier
         __shared__ __align__(8) uint64_t bar;
@@ -124,25 +129,54 @@ k_req_place(const u64* __restrict__ req, uint32_t n_pods, uint32_t n_slices, con
 }
 
 // compact, step 3: one thread per node: key from the node's used[] row, rank = #{sorted requests <= key}
-// by binary search (the 10k sorted requests stay in L1/L2).  The threads also re-arm the duplicate
-// counters for the next call.
+// by binary search.  Every block first brings the sorted requests (<= 96 KB) into shared memory with one bulk
+// asynchronous copy: fourteen dependent loads from shared memory instead of from L2.  The threads also re-arm the
+// duplicate counters for the next call.
 __global__ void __launch_bounds__(256)
 k_node_rank(const u64* __restrict__ sorted, uint32_t n_pods, uint32_t* __restrict__ dup, const u64* __restrict__ used,
             const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, uint32_t dev_stride,
-            RankDsts dst) {
+            RankDsts dst, const uint16_t* __restrict__ cut_src, uint16_t* __restrict__ cut_dst) {
+    extern __shared__ __align__(16) u64 s_sorted[];
+    __shared__ __align__(8) uint64_t bar;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     pdl_launch_dependents();
+    const uint32_t bar_addr = (uint32_t)__cvta_generic_to_shared(&bar);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     bool eligible = false;
     const u64 key = node_key(used, cap, nodeinfo, n_nodes, dev_stride, i, &eligible);  // independent of the request side
     pdl_wait();  // the sorted requests
+    if (threadIdx.x == 0) {
+        const uint32_t bytes = ((n_pods + 1u) & ~1u) * 8u;  // whole 16-byte units (the array has room for GS_MAX_BATCH)
+        asm volatile("fence.proxy.async;" ::: "memory");    // the copy reads what the previous kernel's threads wrote
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(s_sorted)),
+                     "l"(sorted), "r"(bytes), "r"(bar_addr)
+                     : "memory");
+    }
     if (i < n_pods) dup[i] = 0;
+    // results that go to host memory leave from this kernel only (one flush over PCIe at its end, not one per kernel)
+    if (cut_dst && i < n_pods) cut_dst[i] = cut_src[i];
+    __syncthreads();  // the barrier is initialised before anybody waits on it
+    {
+        uint32_t done = 0;
+        while (!done)
+            asm volatile(
+                "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}\n"
+                : "=r"(done)
+                : "r"(bar_addr)
+                : "memory");
+    }
     if (i >= dst.count) return;
     uint32_t lo = 0;
     if (eligible) {  // (false beyond the nodes: the padding of a shard's slice is written as zero)
         uint32_t len = n_pods;
         while (len > 0) {
             const uint32_t half = len >> 1;
-            if (__ldg(sorted + lo + half) <= key) {
+            if (s_sorted[lo + half] <= key) {
                 lo += half + 1;
                 len -= half + 1;
             } else {
@@ -196,7 +230,7 @@ static cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, 
 cudaError_t launch_compact(const u64* d_req, uint32_t n_pods, u64* d_slices, u64* d_sorted, uint32_t* d_dup,
                            const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo, uint32_t n_nodes,
                            uint32_t dev_stride, const RankDsts& dsts, uint16_t* d_cutoff, int sm_count, cudaStream_t st,
-                           uint32_t* n_launches) {
+                           uint32_t* n_launches, u64* d_req_copy, uint16_t* d_cut_tmp) {
     *n_launches = 0;
     if (n_pods == 0 || n_pods > GS_MAX_BATCH) return cudaErrorInvalidValue;
     (void)sm_count;
@@ -209,20 +243,25 @@ cudaError_t launch_compact(const u64* d_req, uint32_t n_pods, u64* d_slices, u64
         const int max_smem = (int)(kMaxSlices * kSlice * sizeof(u64));  // 96 KB: all slices
         cudaError_t ea = cudaFuncSetAttribute(k_req_place, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (ea != cudaSuccess) return ea;
+        ea = cudaFuncSetAttribute(k_node_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (ea != cudaSuccess) return ea;
         if (dev >= 0 && dev < 64) attrs_done[dev] = true;
     }
-    k_slice_sort<<<n_slices, kSlice, 0, st>>>(d_req, n_pods, d_slices);
+    // d_req_copy / d_cut_tmp: given when the requests and the cutoffs live in (page-locked) host memory
+    k_slice_sort<<<n_slices, kSlice, 0, st>>>(d_req, n_pods, d_slices, d_req_copy);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     ++*n_launches;
     // small blocks: the searches of a pod are latency, so they are spread over as many SMs as there are blocks
-    e = launch_pdl(k_req_place, dim3((n_pods + 63) / 64), dim3(64), (size_t)n_slices * kSlice * sizeof(u64), st, d_req, n_pods,
-                   n_slices, (const u64*)d_slices, d_dup, d_sorted, d_cutoff);
+    e = launch_pdl(k_req_place, dim3((n_pods + 63) / 64), dim3(64), (size_t)n_slices * kSlice * sizeof(u64), st,
+                   d_req_copy ? (const u64*)nullptr : d_req, (const u64*)d_req_copy, n_pods, n_slices, (const u64*)d_slices, d_dup,
+                   d_sorted, d_cut_tmp ? d_cut_tmp : d_cutoff);
     if (e != cudaSuccess) return e;
     ++*n_launches;
     const uint32_t n_threads = dsts.count > n_pods ? dsts.count : n_pods;
-    e = launch_pdl(k_node_rank, dim3((n_threads + 255) / 256), dim3(256), 0, st, (const u64*)d_sorted,
-                   n_pods, d_dup, d_used, d_cap, d_nodeinfo, n_nodes, dev_stride, dsts);
+    e = launch_pdl(k_node_rank, dim3((n_threads + 255) / 256), dim3(256), (size_t)((n_pods + 1u) & ~1u) * sizeof(u64), st, (const u64*)d_sorted,
+                   n_pods, d_dup, d_used, d_cap, d_nodeinfo, n_nodes, dev_stride, dsts, (const uint16_t*)d_cut_tmp,
+                   d_cut_tmp ? d_cutoff : (uint16_t*)nullptr);
     if (e != cudaSuccess) return e;
     ++*n_launches;
     return cudaSuccess;

@@ -67,7 +67,8 @@ struct RankDsts {
 cudaError_t launch_compact(const unsigned long long* d_req, uint32_t n_pods, unsigned long long* d_slices, unsigned long long* d_sorted,
                            uint32_t* d_dup, const unsigned long long* d_used, const unsigned long long* d_cap,
                            const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, const RankDsts& dsts,
-                           uint16_t* d_cutoff, int sm_count, cudaStream_t st, uint32_t* n_launches);
+                           uint16_t* d_cutoff, int sm_count, cudaStream_t st, uint32_t* n_launches,
+                           unsigned long long* d_req_copy = nullptr, uint16_t* d_cut_tmp = nullptr);
 // bit c of row p = predicate(pod p, node subset[c]); one launch
 cudaError_t launch_filter_subset(const unsigned long long* d_req, uint32_t n_pods, const uint32_t* d_subset, uint32_t n_cand,
                                  const unsigned long long* d_used, const unsigned long long* d_cap,

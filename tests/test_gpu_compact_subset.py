@@ -181,3 +181,51 @@ def test_compact_gather_entry_point_writes_every_destination():
         assert (d_cut.cpu().numpy().view(np.uint16) == 1 + np.searchsorted(srt, reqs, side="left")).all()
         with pytest.raises(gsx.GpushareError):
             s.filter_batch_compact_device_gather(d_req.data_ptr(), P, [dsts[0].data_ptr()], 0, sc.n_nodes - 1, d_cut.data_ptr(), 0)
+
+
+def test_compact_with_page_locked_buffers_is_the_same_answer():
+    """With page-locked caller buffers the kernels read the requests and write rank[] / cutoff[] in the caller's memory
+    directly (no staging copies); the answer must be the one the staged path gives, for one chunk, for several chunks,
+    for a sub-array of a larger page-locked block, after a state change, and when only some of the three buffers are
+    page-locked (staged path again)."""
+    sc = synth.make_config("C3")
+    cap, used, ndev, cls, recs = H.soa_state(sc)
+    rng = np.random.default_rng(12)
+    N = sc.n_nodes
+    with H.load_snapshot(sc, extra_pods=2048) as s:
+        for P in (1, 777, gsx.capi.MAX_BATCH, gsx.capi.MAX_BATCH + 5000):
+            reqs = hard_requests(max(P, 40), rng)[:P]
+            chunks = (P + gsx.capi.MAX_BATCH - 1) // gsx.capi.MAX_BATCH
+            want_rank, want_cut = s.filter_batch_compact(reqs)                     # pageable numpy arrays: staged
+            h_req = gsx.PinnedBuffer(P + 3, np.uint64)
+            h_rank = gsx.PinnedBuffer((chunks + 1, N), np.uint16)
+            h_cut = gsx.PinnedBuffer(P + 8, np.uint16)
+            h_req.array[3:] = reqs
+            h_rank.array[:] = 0xABCD
+            h_cut.array[:] = 0xABCD
+            rank, cut = s.filter_batch_compact(h_req.array[3:], out_rank=h_rank.array[1:], out_cutoff=h_cut.array[8:])
+            assert (rank == want_rank).all() and (cut == want_cut).all(), P
+            assert (h_rank.array[0] == 0xABCD).all() and (h_cut.array[:8] == 0xABCD).all()   # nothing else touched
+            # mixed: only the requests page-locked
+            rank2, cut2 = s.filter_batch_compact(h_req.array[3:])
+            assert (rank2 == want_rank).all() and (cut2 == want_cut).all()
+            for b in (h_req, h_rank, h_cut):
+                b.free()
+        # a write between two page-locked calls is seen by the second
+        P = 3000
+        reqs = hard_requests(P, rng)
+        h_req = gsx.PinnedBuffer(P, np.uint64)
+        h_rank = gsx.PinnedBuffer((1, N), np.uint16)
+        h_cut = gsx.PinnedBuffer(P, np.uint16)
+        h_req.array[:] = reqs
+        s.filter_batch_compact(h_req.array, out_rank=h_rank.array, out_cutoff=h_cut.array)
+        table = np.zeros(sc.n_pods + 2048, synth.POD_DT)
+        table[: sc.n_pods] = recs
+        table["flags"][: sc.n_pods][~S.legal(recs, ndev)] = 0
+        ev = synth.add_events(sc.n_pods + np.arange(600), rng.integers(0, N, 600), rng.integers(0, 8, 600),
+                              rng.choice(synth.CATALOGUE[3:8], 600))
+        S.apply_events(ev, table, used, ndev)
+        s.pods_apply_async(ev)
+        rank, cut = s.filter_batch_compact(h_req.array, out_rank=h_rank.array, out_cutoff=h_cut.array)
+        key, elig = S.node_keys(cap, used, ndev, cls)
+        assert ((rank[0][None, :] >= cut[:, None]) == S.filter_pass(reqs, key, elig)).all()
