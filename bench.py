@@ -725,6 +725,64 @@ def run_product(args):
         sub_lat[f"1_pod_x_{C}_candidates_us"] = {"p50": 1e6 * _pct(ts, 0.5), "p99": 1e6 * _pct(ts, 0.99)}
     e2e_subset = {"latency": sub_lat, "api": "gs_filter_batch_subset (pkg/scheduler/predicate.go:21: the candidate list of one request)"}
 
+    # the same compact call from three host threads at once, each with its own page-locked buffers (the extender's HTTP
+    # handlers are concurrent; the library gives each caller a filter context of its own): calls per second of all of them
+    def _concurrent(n_threads, steps):
+        bufs = []
+        for _ in range(n_threads):
+            r = gsx.PinnedBuffer(P, np.uint64)
+            r.array[:] = reqs
+            bufs.append((r, gsx.PinnedBuffer((1, N), np.uint16), gsx.PinnedBuffer(P, np.uint16)))
+        start = threading.Barrier(n_threads + 1)
+        errs = []
+
+        def work(b):
+            try:
+                for _ in range(3):
+                    snap.filter_batch_compact(b[0].array, out_rank=b[1].array, out_cutoff=b[2].array)
+                start.wait()
+                for _ in range(steps):
+                    snap.filter_batch_compact(b[0].array, out_rank=b[1].array, out_cutoff=b[2].array)
+            except Exception as ex:  # report, do not hide
+                errs.append(repr(ex))
+                try:
+                    start.abort()
+                except Exception:
+                    pass
+
+        ths = [threading.Thread(target=work, args=(b,)) for b in bufs]
+        for t in ths:
+            t.start()
+        start.wait()
+        t0 = time.perf_counter()
+        for t in ths:
+            t.join()
+        dt = time.perf_counter() - t0
+        same = all(bool((b[1].array == h_rank.array).all() and (b[2].array == h_cut.array).all()) for b in bufs)
+        for b in bufs:
+            for x in b:
+                x.free()
+        return dt, same, errs
+
+    try:
+        n_thr = 3
+        dts = []
+        same_all = True
+        for _ in range(e2e_rep):
+            tm.fence()
+            dt, same, errs = _concurrent(n_thr, e2e_steps * 5)
+            if errs:
+                raise RuntimeError("; ".join(errs))
+            same_all &= same
+            dts.append(tm.max_over_ranks(1e3 * dt) / (n_thr * e2e_steps * 5))
+        sp_t = _spread(dts)
+        extra["e2e_compact_concurrent"] = {"value": world * P * N / (sp_t["median"] * 1e-3), "unit": UNIT, "threads": n_thr,
+                                           "ms_per_call_aggregate": sp_t["median"], "ms_min": sp_t["min"], "ms_max": sp_t["max"],
+                                           "calls_per_thread": e2e_steps * 5, "repeats": e2e_rep, "same_answer_in_every_thread": same_all,
+                                           "h2d_bytes_per_step": P * 8, "d2h_bytes_per_step": N * 2 + P * 2}
+    except Exception as ex:  # report, do not hide
+        extra["e2e_compact_concurrent"] = {"error": repr(ex)}
+
     # ---- config 5: churn replay on the paced schedule (single GPU) ----
     if world == 1 and not args.no_churn:
         try:
