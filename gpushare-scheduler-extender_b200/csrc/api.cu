@@ -822,6 +822,33 @@ int gs_filter_batch_subset(gs_snapshot* s, const uint64_t* req, uint32_t n_pods,
     }
     const size_t req_bytes = ((size_t)n_pods * sizeof(u64) + 255) & ~(size_t)255;
     const size_t sub_bytes = (size_t)n_candidates * sizeof(uint32_t);
+    // A small request -- what kube-scheduler sends: one pod, a list of candidate names -- goes through the context's
+    // page-locked block alone: inputs copied there by the CPU, the kernel reads them and writes the answer in place over
+    // PCIe, one wait, no DMA set up at all (three copies cost more than the kernel: 38 -> ~15 us per call).
+    {
+        const size_t sub_pad = (sub_bytes + 255) & ~(size_t)255;
+        const size_t total = req_bytes + sub_pad + out_bytes;
+        if (n_pods <= 64 && total <= (64u << 10) && !s->profiling) {
+            rc = grow_pinned(s, &c.h_stage, &c.h_stage_bytes, total);
+            if (rc) return rc;
+            rc = order_filter(s, c, c.stream);
+            if (rc) return rc;
+            c.prev_filter = false;
+            char* h = static_cast<char*>(c.h_stage);
+            memcpy(h, req, (size_t)n_pods * sizeof(u64));
+            memcpy(h + req_bytes, node_subset, sub_bytes);
+            if (row_stride_words > words) memset(h + req_bytes + sub_pad, 0, out_bytes);
+            cudaError_t e = gs::launch_filter_subset(reinterpret_cast<const u64*>(h), n_pods,
+                                                     reinterpret_cast<const uint32_t*>(h + req_bytes), n_candidates, s->d_used,
+                                                     s->d_cap, s->d_nodeinfo, s->n_nodes, s->max_devs,
+                                                     reinterpret_cast<uint32_t*>(h + req_bytes + sub_pad), row_stride_words, c.stream);
+            if (e != cudaSuccess) return cuda_fail(s, e, "kernel launch");
+            s->launches += 1;
+            CU(cudaStreamSynchronize(c.stream));
+            memcpy(out_bitmap, h + req_bytes + sub_pad, out_bytes);
+            return GS_OK;
+        }
+    }
     rc = grow_device(s, &c.d_stage, &c.d_stage_bytes, req_bytes + sub_bytes, true);
     if (rc) return rc;
     rc = grow_device(s, &c.d_bitmap, &c.d_bitmap_bytes, out_bytes, false);
