@@ -993,6 +993,11 @@ int gs_node_classes(gs_snapshot* s, uint8_t* out_class, uint32_t n) {
     return GS_OK;
 }
 
+#ifndef GS_BIND_IN_PLACE_MAX
+#define GS_BIND_IN_PLACE_MAX 1024
+#endif
+constexpr uint32_t kBindInPlaceMax = GS_BIND_IN_PLACE_MAX;
+
 int gs_bind_batch(gs_snapshot* s, const gs_bind_req* binds, uint32_t n, int32_t* out_dev) {
     if (!s || ((!binds || !out_dev) && n)) return fail(GS_ERR_INVALID, "null argument");
     WriteLock lk(s->state_mu);
@@ -1027,17 +1032,33 @@ int gs_bind_batch(gs_snapshot* s, const gs_bind_req* binds, uint32_t n, int32_t*
         gs_bind_req* d_binds = reinterpret_cast<gs_bind_req*>(s->d_stage);
         int32_t* d_out = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(s->d_stage) + out_off);
         memcpy(h, binds + b0, in_bytes);
-        CU(cudaMemcpyAsync(d_binds, h, in_bytes, cudaMemcpyHostToDevice, s->stream));
-        rc = timed(s, GS_K_BIND_SORT, s->stream, 1, [&] {
-            return gs::launch_sort_binds(s->device, d_binds, m, s->d_bind_keys, s->d_bind_perm, s->stream);
-        });
-        if (rc) return rc;
-        rc = timed(s, GS_K_BIND_SCAN, s->stream, 1, [&] {
-            return gs::launch_bind_scan(d_binds, m, s->d_bind_keys, s->d_bind_perm, s->d_pods, s->max_pods, s->d_nodeinfo,
-                                        s->n_nodes, s->d_cap, s->max_devs, s->d_used, d_out, s->stream);
-        });
-        if (rc) return rc;
-        CU(cudaMemcpyAsync(h + out_off, d_out, out_bytes, cudaMemcpyDeviceToHost, s->stream));
+        // a handful of binds (the extender binds one pod per request): the kernels read them from the page-locked block
+        // and write the chosen devices there, no copies to set up
+        const bool in_place = m <= kBindInPlaceMax && !s->profiling;
+        if (in_place) {
+            d_binds = reinterpret_cast<gs_bind_req*>(h);
+            d_out = reinterpret_cast<int32_t*>(h + out_off);
+        } else {
+            CU(cudaMemcpyAsync(d_binds, h, in_bytes, cudaMemcpyHostToDevice, s->stream));
+        }
+        if (m <= 32) {  // one launch of one warp orders and walks a short queue
+            rc = timed(s, GS_K_BIND_SCAN, s->stream, 1, [&] {
+                return gs::launch_bind_small(d_binds, m, s->d_pods, s->max_pods, s->d_nodeinfo, s->n_nodes, s->d_cap, s->max_devs,
+                                             s->d_used, d_out, s->stream);
+            });
+            if (rc) return rc;
+        } else {
+            rc = timed(s, GS_K_BIND_SORT, s->stream, 1, [&] {
+                return gs::launch_sort_binds(s->device, d_binds, m, s->d_bind_keys, s->d_bind_perm, s->stream);
+            });
+            if (rc) return rc;
+            rc = timed(s, GS_K_BIND_SCAN, s->stream, 1, [&] {
+                return gs::launch_bind_scan(d_binds, m, s->d_bind_keys, s->d_bind_perm, s->d_pods, s->max_pods, s->d_nodeinfo,
+                                            s->n_nodes, s->d_cap, s->max_devs, s->d_used, d_out, s->stream);
+            });
+            if (rc) return rc;
+        }
+        if (!in_place) CU(cudaMemcpyAsync(h + out_off, d_out, out_bytes, cudaMemcpyDeviceToHost, s->stream));
         CU(cudaStreamSynchronize(s->stream));
         memcpy(out_dev + b0, h + out_off, out_bytes);
     }

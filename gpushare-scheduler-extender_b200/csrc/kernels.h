@@ -45,6 +45,9 @@ cudaError_t launch_rebuild(const gs_pod_record* d_pods, uint32_t n_slots, uint32
 cudaError_t launch_apply_events(const gs_pod_event* d_events, uint32_t n, gs_pod_record* d_pods, uint32_t max_pods,
                                 int32_t* d_last_ev, const uint32_t* d_nodeinfo, uint32_t n_nodes,
                                 uint32_t dev_stride, unsigned long long* d_used, cudaStream_t st);
+cudaError_t launch_bind_small(const gs_bind_req* d_binds, uint32_t n, gs_pod_record* d_pods, uint32_t max_pods,
+                              const uint32_t* d_nodeinfo, uint32_t n_nodes, const unsigned long long* d_cap, uint32_t dev_stride,
+                              unsigned long long* d_used, int32_t* d_out_dev, cudaStream_t st);
 cudaError_t launch_bind_scan(const gs_bind_req* d_binds, uint32_t n, const unsigned long long* d_sorted_nodes,
                              const uint16_t* d_perm, gs_pod_record* d_pods, uint32_t max_pods,
                              const uint32_t* d_nodeinfo, uint32_t n_nodes, const unsigned long long* d_cap,

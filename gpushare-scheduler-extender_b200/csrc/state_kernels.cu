@@ -119,12 +119,12 @@ __global__ void k_events_apply(const gs_pod_event* __restrict__ ev, uint32_t n, 
 // ------------------------------------------------------------------------------------------------
 // kRegs: the node's used[] row lives in registers (stride-8 snapshots) for the whole walk and is written
 // back once; otherwise the walk reads and writes the row in global memory.
+// (sorted_nodes / perm: global memory, or the shared memory of the one-warp kernel below)
 template <bool kRegs>
-__global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, const u64* __restrict__ sorted_nodes,
-                            const uint16_t* __restrict__ perm, gs_pod_record* pods, uint32_t max_pods,
-                            const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, const u64* __restrict__ cap,
-                            uint32_t dev_stride, u64* used, int32_t* __restrict__ out_dev) {
-    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void bind_walk(uint32_t j, const gs_bind_req* __restrict__ binds, uint32_t n, const u64* sorted_nodes,
+                                          const uint16_t* perm, gs_pod_record* pods, uint32_t max_pods,
+                                          const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, const u64* __restrict__ cap,
+                                          uint32_t dev_stride, u64* used, int32_t* __restrict__ out_dev) {
     if (j >= n) return;
     const u64 node64 = sorted_nodes[j];
     if (j > 0 && sorted_nodes[j - 1] == node64) return;  // not the head of its node's run
@@ -218,6 +218,41 @@ __global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, c
     }
 }
 
+template <bool kRegs>
+__global__ void k_bind_scan(const gs_bind_req* __restrict__ binds, uint32_t n, const u64* __restrict__ sorted_nodes,
+                            const uint16_t* __restrict__ perm, gs_pod_record* pods, uint32_t max_pods,
+                            const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, const u64* __restrict__ cap,
+                            uint32_t dev_stride, u64* used, int32_t* __restrict__ out_dev) {
+    bind_walk<kRegs>(blockIdx.x * blockDim.x + threadIdx.x, binds, n, sorted_nodes, perm, pods, max_pods, nodeinfo, n_nodes, cap,
+                     dev_stride, used, out_dev);
+}
+
+// A queue of at most 32 binds (the extender binds one pod per request) in ONE launch of one warp: every lane counts the
+// binds that go before its own (by node, then by position: the stable order the radix sort gives), the order goes to
+// shared memory, and the lanes that head a node's run walk it.
+template <bool kRegs>
+__global__ void __launch_bounds__(32)
+k_bind_small(const gs_bind_req* __restrict__ binds, uint32_t n, gs_pod_record* pods, uint32_t max_pods,
+             const uint32_t* __restrict__ nodeinfo, uint32_t n_nodes, const u64* __restrict__ cap, uint32_t dev_stride, u64* used,
+             int32_t* __restrict__ out_dev) {
+    __shared__ u64 s_nodes[32];
+    __shared__ uint16_t s_perm[32];
+    const uint32_t lane = threadIdx.x;
+    const u64 key = lane < n ? (u64)binds[lane].node_idx : ~0ull;
+    uint32_t before = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 32; ++j) {
+        const u64 other = __shfl_sync(0xffffffffu, key, j);
+        before += (j < n && (other < key || (other == key && j < lane))) ? 1u : 0u;
+    }
+    if (lane < n) {
+        s_nodes[before] = key;
+        s_perm[before] = (uint16_t)lane;
+    }
+    __syncwarp();
+    bind_walk<kRegs>(lane, binds, n, s_nodes, s_perm, pods, max_pods, nodeinfo, n_nodes, cap, dev_stride, used, out_dev);
+}
+
 // ------------------------------------------------------------------------------------------------
 cudaError_t launch_fill_i32(int32_t* d, int32_t v, size_t n, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
@@ -272,6 +307,17 @@ cudaError_t launch_apply_events(const gs_pod_event* d_events, uint32_t n, gs_pod
     k_events_mark<<<blocks, 256, 0, st>>>(d_events, n, max_pods, d_last_ev, d_nodeinfo, n_nodes, dev_stride);
     k_events_apply<<<blocks, 256, 0, st>>>(d_events, n, d_pods, max_pods, d_last_ev, d_nodeinfo, n_nodes, dev_stride,
                                            d_used);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bind_small(const gs_bind_req* d_binds, uint32_t n, gs_pod_record* d_pods, uint32_t max_pods,
+                              const uint32_t* d_nodeinfo, uint32_t n_nodes, const u64* d_cap, uint32_t dev_stride, u64* d_used,
+                              int32_t* d_out_dev, cudaStream_t st) {
+    if (n == 0 || n > 32) return cudaErrorInvalidValue;
+    if (dev_stride == 8)
+        k_bind_small<true><<<1, 32, 0, st>>>(d_binds, n, d_pods, max_pods, d_nodeinfo, n_nodes, d_cap, dev_stride, d_used, d_out_dev);
+    else
+        k_bind_small<false><<<1, 32, 0, st>>>(d_binds, n, d_pods, max_pods, d_nodeinfo, n_nodes, d_cap, dev_stride, d_used, d_out_dev);
     return cudaGetLastError();
 }
 

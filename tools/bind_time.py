@@ -12,7 +12,7 @@ snap = gsx.Snapshot(sc.n_nodes, sc.max_devs, sc.n_pods + 200000)
 snap.node_upsert(sc.gs_nodes()); snap.pods_load(sc.gs_pod_records()); snap.rebuild()
 rng = np.random.default_rng(0)
 slot = sc.n_pods
-for B in (1, 200, 2048):
+for B in (1, 16, 200, 2048):
     for prof in (False, True):
         snap.profile(prof); snap.profile_reset()
         ts = []
@@ -24,6 +24,7 @@ for B in (1, 200, 2048):
         line = f"B={B} profiling={prof}: wall p50 {1e6*ts[len(ts)//2]:.1f} us"
         if prof:
             pr = snap.profile_read()
-            line += f"; device: sort {1e3*pr['bind_sort'][1]/pr['bind_sort'][0]:.1f} us, scan {1e3*pr['bind_scan'][1]/pr['bind_scan'][0]:.1f} us"
+            per = lambda k: f"{1e3*pr[k][1]/pr[k][0]:.1f} us" if pr[k][0] else "-"   # (a queue of <= 32 binds is one launch)
+            line += f"; device: sort {per('bind_sort')}, scan {per('bind_scan')}"
         print(line)
 snap.close()
