@@ -203,7 +203,10 @@ int gs_filter_batch_subset(gs_snapshot* s, const uint64_t* req, uint32_t n_pods,
  * that can never pass; cutoff[p] = 1 + how many requests of the chunk are smaller than pod p's).  Ranks are
  * relative to a chunk of GS_MAX_BATCH pods: out_rank is [ceil(n_pods / GS_MAX_BATCH)][rank_stride] with
  * rank_stride >= node count (padding written as zero), out_cutoff is [n_pods].  2 bytes per node and per pod
- * cross PCIe instead of one bit per (pod, node); the caller expands what it needs. */
+ * cross PCIe instead of one bit per (pod, node); the caller expands what it needs.  When req, out_rank and
+ * out_cutoff are page-locked (gs_host_alloc, or cudaHostAlloc / cudaHostRegister by the caller) and rank_stride
+ * equals the node count, the kernels read and write them in place and no copy is set up; the call still returns
+ * with the results in the caller's memory. */
 int gs_filter_batch_compact(gs_snapshot* s, const uint64_t* req, uint32_t n_pods, uint16_t* out_rank,
                             uint32_t rank_stride, uint16_t* out_cutoff);
 /* Same with device buffers, asynchronous on `cuda_stream` (padding of d_out_rank is left untouched). */
@@ -249,7 +252,8 @@ int gs_inspect(gs_snapshot* s, uint32_t node_idx, uint64_t* out_capacity, uint64
 int gs_read_used(gs_snapshot* s, uint32_t first_node, uint32_t n, uint64_t* out_used);
 int gs_read_pods(gs_snapshot* s, uint32_t first_slot, uint32_t n, gs_pod_record* out);
 
-/* Pinned host memory for bitmaps / requests (lets copies run at full PCIe rate). */
+/* Page-locked host memory for bitmaps / requests / ranks: copies run at full PCIe rate, and the compact Filter works
+ * on such buffers in place.  Blocks from here are recognised without a driver call. */
 int gs_host_alloc(size_t bytes, void** out);
 int gs_host_free(void* p);
 
