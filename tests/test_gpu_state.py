@@ -104,6 +104,38 @@ def test_bind_batch_matches_sequential_binpack(hot):
         assert (s.read_used() == used).all()
 
 
+def test_bind_calls_of_every_size_match_sequential_binpack():
+    """gs_bind_batch takes three routes by queue length: one launch of one warp (<= 32 binds), the two kernels on the
+    page-locked block in place (<= 1024), the two kernels on a device copy (more).  A long run of calls of mixed
+    lengths, many binds per node (so queue order inside a node matters), must leave exactly what sequential binds do."""
+    sc = synth.make_cluster(64, 8, 16384, running=300, seed=21, quirks=True, fill=0.6)
+    cap, used, ndev, cls, recs = H.soa_state(sc)
+    rng = np.random.default_rng(21)
+    sizes = [1, 1, 2, 3, 31, 32, 33, 64, 200, 1, 1024, 1025, 32, 7, 1500, 1]
+    total = sum(sizes)
+    table = np.zeros(sc.n_pods + total, synth.POD_DT)
+    table[: sc.n_pods] = recs
+    table["flags"][: sc.n_pods][~S.legal(recs, ndev)] = 0
+    with H.load_snapshot(sc, extra_pods=total) as s:
+        slot = sc.n_pods
+        for B in sizes:
+            nodes = rng.integers(0, sc.n_nodes + 2, B)            # two names outside the snapshot: NODE_NOT_FOUND
+            reqs = rng.choice(np.r_[synth.CATALOGUE[:6], [0, -5, 1, 16384]], B).astype(np.int64)
+            binds = synth.bind_records(nodes, reqs, first_slot=slot, counted=rng.random(B) < 0.9)
+            if B >= 3:
+                binds["slot"][2] = sc.n_pods                       # a slot that already holds an entry (first call: fresh)
+                if len(np.unique(binds["slot"])) != B:
+                    binds["slot"][2] = slot + 2
+            slot += B
+            want = S.bind_sequential(binds, cap, used, ndev, cls, table)
+            got = s.bind_batch(binds)
+            assert (got == want).all(), B
+            assert (s.read_used() == used).all(), B
+        assert (s.read_pods(0, sc.n_pods + total) == table).all()
+        s.rebuild()
+        assert (s.read_used() == used).all()
+
+
 def test_ka2_bind_through_the_abi():
     # docs/designs/designs.md:80
     with gsx.Snapshot(1, 4, 8) as s:
