@@ -40,7 +40,7 @@ EXPORTS = [
     "gs_read_used", "gs_read_pods", "gs_host_alloc", "gs_host_free", "gs_profile_enable", "gs_profile_read",
     "gs_profile_reset", "gs_launch_count", "gs_device_ptrs", "gs_pods_apply_static", "gs_set_option",
     "gs_pods_apply_async", "gs_snapshot_sync", "gs_snapshot_external_write", "gs_filter_batch_subset",
-    "gs_filter_batch_compact", "gs_filter_batch_compact_device", "gs_sm_count", "gs_filter_batch_compact_device_gather",
+    "gs_filter_batch_compact", "gs_filter_batch_compact_device", "gs_sm_count", "gs_filter_batch_compact_device_gather", "gs_debug_early_starts",
 ]
 
 
@@ -105,6 +105,7 @@ def load():
         "gs_filter_batch_compact": (C.c_int, [vp, vp, u32, vp, u32, vp]),
         "gs_filter_batch_compact_device": (C.c_int, [vp, vp, u32, vp, u32, vp, vp]),
         "gs_sm_count": (C.c_int, [vp, C.POINTER(C.c_int)]),
+        "gs_debug_early_starts": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
         "gs_filter_batch_compact_device_gather": (C.c_int, [vp, vp, u32, C.POINTER(vp), u32, u32, u32, vp, vp]),
     }
     for name, (res, args) in sig.items():
@@ -353,6 +354,13 @@ class Snapshot:
     def sm_count(self) -> int:
         v = C.c_int()
         _check(load().gs_sm_count(self.h, C.byref(v)))
+        return v.value
+
+    @property
+    def early_starts(self) -> int:
+        """CTAs of the expansion kernel that found their batch's preparation unfinished (expected 0); waits for the GPU."""
+        v = C.c_uint64()
+        _check(load().gs_debug_early_starts(self.h, C.byref(v)))
         return v.value
 
     @property

@@ -298,7 +298,7 @@ int alloc_ctx(gs_snapshot* s, FilterCtx& c) {
     CU(cudaMalloc(&c.d_node_key, 2 * (size_t)s->rank_words * 32 * sizeof(u64)));
     CU(cudaMalloc(&c.d_node_key32, 2 * (size_t)s->rank_words * 32 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_sched, 4 * sizeof(uint32_t)));
-    CU(cudaMalloc(&c.d_epochs, 6 * sizeof(uint32_t)));
+    CU(cudaMalloc(&c.d_epochs, 8 * sizeof(uint32_t)));
     CU(cudaMalloc(&c.d_cslices, (B + 1024) * sizeof(u64)));
     CU(cudaMalloc(&c.d_csorted, B * sizeof(u64)));
     CU(cudaMalloc(&c.d_cdup, B * sizeof(uint32_t)));
@@ -306,7 +306,7 @@ int alloc_ctx(gs_snapshot* s, FilterCtx& c) {
     CU(cudaMalloc(&c.d_ccut, B * sizeof(uint16_t)));
     CU(cudaMemsetAsync(c.d_pod_hist, 0, 2 * 512 * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_sched, 0, 4 * sizeof(uint32_t), s->stream));
-    CU(cudaMemsetAsync(c.d_epochs, 0, 6 * sizeof(uint32_t), s->stream));
+    CU(cudaMemsetAsync(c.d_epochs, 0, 8 * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_cdup, 0, B * sizeof(uint32_t), s->stream));
     CU(cudaMemsetAsync(c.d_rank_planes, 0, 2 * (size_t)s->rank_words * gs::kRankPlanes * sizeof(uint32_t), s->stream));
     return GS_OK;
@@ -360,6 +360,7 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     fb.prep_epoch = c.d_epochs + 3 * set + 1;
     fb.expand_epoch = c.d_epochs + 3 * set + 2;
     fb.fault = s->d_fault;
+    fb.early_starts = c.d_epochs + 6;
     // With GS_OPT_PIPELINE_FILTERS, a filter that directly follows another filter of this context on the same
     // stream, writing somewhere else, does not wait for that filter's expand kernel to drain before its own prep
     // kernel starts (the two touch different work-buffer sets).  Anything else keeps plain stream order.
@@ -1188,6 +1189,21 @@ int gs_launch_count(gs_snapshot* s, uint64_t* out_launches) {
 int gs_sm_count(gs_snapshot* s, int* out_sms) {
     if (!s || !out_sms) return fail(GS_ERR_INVALID, "null argument");
     *out_sms = s->sm_count;
+    return GS_OK;
+}
+int gs_debug_early_starts(gs_snapshot* s, uint64_t* out_count) {
+    if (!s || !out_count) return fail(GS_ERR_INVALID, "null argument");
+    *out_count = 0;
+    WriteLock lk(s->state_mu);  // (nothing else of the snapshot is in a call)
+    int rc = use_device(s);
+    if (rc) return rc;
+    CU(cudaDeviceSynchronize());
+    for (FilterCtx& c : s->ctx) {
+        uint32_t v = 0;
+        if (!c.d_epochs) continue;
+        CU(cudaMemcpy(&v, c.d_epochs + 6, sizeof(v), cudaMemcpyDeviceToHost));
+        *out_count += v;
+    }
     return GS_OK;
 }
 int gs_device_ptrs(gs_snapshot* s, void** d_used, void** d_capacity, void** d_nodeinfo, void** d_pods) {

@@ -25,6 +25,7 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     uint32_t* expand_epoch;           // [1] completed k_expand launches on this buffer set
     uint32_t set_index;               // 0 / 1: which of the two buffer sets this is (development traces)
     unsigned int* fault;              // mapped host word: where a kernel gave up a bounded wait (may be null)
+    uint32_t* early_starts;           // [1] CTAs of k_expand that found their batch's k_prep unfinished (expected: 0)
 };
 cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n, unsigned long long* d_sorted,
                               uint16_t* d_perm, cudaStream_t st);

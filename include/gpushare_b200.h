@@ -279,6 +279,12 @@ int gs_launch_count(gs_snapshot* s, uint64_t* out_launches);
 /* SMs the kernels size their grids for: those of the CUDA context that was current when the snapshot was
  * created (fewer than the device has inside a green context or an MPS partition). */
 int gs_sm_count(gs_snapshot* s, int* out_sms);
+/* Diagnostics.  With overlapping Filter batches a CTA of the expansion kernel takes its batch's preparation kernel to be
+ * complete from the order of the launches and only confirms it by an epoch it reads while its first inputs are on their
+ * way; a CTA that finds the epoch not reached waits for it and asks again (the results are right either way).  This is
+ * how many CTAs did so since the snapshot was created: 0 unless the launch order is not what the library produces.
+ * Waits for the GPU. */
+int gs_debug_early_starts(gs_snapshot* s, uint64_t* out_count);
 /* Device pointers of the snapshot arrays, for zero-copy use from the same process (tests, NCCL). */
 int gs_device_ptrs(gs_snapshot* s, void** d_used, void** d_capacity, void** d_nodeinfo, void** d_pods);
 /* Tell the snapshot that work queued on `cuda_stream` by the caller (a kernel of its own, gs_pods_apply_static)

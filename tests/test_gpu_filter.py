@@ -1,5 +1,7 @@
 """K3 parity: gs_filter_batch (through the C ABI) against the CPU oracle.
 Bit-exact: every word of the bitmap must equal the oracle's pass set."""
+import os
+
 import numpy as np
 import pytest
 
@@ -284,3 +286,8 @@ def test_pipelined_c4_hard_request_distributions():
             got = o.cpu().numpy().view(np.uint32)
             want = S.pack_bitmap(S.filter_pass(b, key, elig), stride)
             assert (got == want).all(), i
+        # Overlapping batches: the expansion kernel's CTAs take their batch's preparation to be complete from the launch
+        # order and confirm it by an epoch; none may ever find it unreached.  (A build with -DGS_TEST_FORCE_EARLY_START
+        # pretends an eighth of them do: the same bitmaps must come out, through the wait-and-ask-again path.)
+        forced = os.environ.get("GS_EXPECT_EARLY_STARTS", "0") == "1"
+        assert (s.early_starts > 0) if forced else (s.early_starts == 0)
