@@ -378,14 +378,14 @@ int filter_chunk(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods
     if (do_pods || do_nodes)
         rc = timed(s, do_pods ? GS_K_SORT : GS_K_NODE_RANK, st, 1, [&] {
             cudaError_t e = gs::launch_prep(d_req, n_pods, do_pods, do_nodes, shift, fb, s->d_used, s->d_cap, s->d_nodeinfo,
-                                            s->n_nodes, s->max_devs, words_pad, overlap_ok, c.n_expand[set], st);
+                                            s->n_nodes, s->max_devs, words_pad, overlap_ok, c.n_expand[set], &c.n_prep_blocks[set], st);
             if (e == cudaSuccess) ++c.n_prep[set];
             return e;
         });
     if (rc) return rc;
     if (stages & GS_STAGE_EXPAND)
         rc = timed(s, GS_K_EXPAND, st, 1, [&] {
-            cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, c.n_prep[set], st);
+            cudaError_t e = gs::launch_expand(s->sm_count, fb, n_pods, words, row_stride, d_out, overlap_ok, c.n_prep[set], c.n_prep_blocks[set], st);
             if (e == cudaSuccess) ++c.n_expand[set];
             return e;
         });

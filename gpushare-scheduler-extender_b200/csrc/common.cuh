@@ -89,8 +89,11 @@ struct FilterCtx {
     unsigned long long* d_node_key = nullptr;     // [2][rank_words * 32]
     uint32_t* d_node_key32 = nullptr;             // [2][rank_words * 32]
     uint32_t* d_sched = nullptr;                  // [2][2] tile scheduler of k_expand (self re-arming)
-    uint32_t* d_epochs = nullptr;  // per set s: [3 * s] finished k_prep blocks, [3 * s + 1] k_prep epoch, [3 * s + 2] k_expand epoch
+    // per set s: [3 * s] finished k_prep blocks (all launches), [3 * s + 1] k_prep epoch, [3 * s + 2] k_expand epoch;
+    // [6] CTAs of k_expand that started before their k_prep's blocks had all finished (diagnostic)
+    uint32_t* d_epochs = nullptr;
     uint32_t fb_set = 0;
+    uint32_t n_prep_blocks[2] = {0, 0};  // what the set's count of finished k_prep blocks will reach
     uint32_t n_prep[2] = {0, 0};      // what the set's k_prep / k_expand epochs will reach when everything issued has run
     uint32_t n_expand[2] = {0, 0};
     bool prev_filter = false;            // the last operation enqueued for this context was a full filter ...

@@ -291,6 +291,11 @@ __device__ __forceinline__ void wait_epoch(const uint32_t* p, uint32_t want, uns
 // so a CTA of k_expand that starts knows them complete without reading an epoch first (0: k_prep triggers at its start
 // and every CTA of k_expand polls the epoch before it asks for its first tile: one more round trip per CTA, 14.6 us per
 // step instead of 13.9).
+// (1: from a CTA's second tile on the ticket is taken at the top of the tile -- measured slower: 14.2 vs 14.0 us per step,
+// 16.4 vs 15.5 us alone; profiles/NOTES.md 34)
+#ifndef GS_EARLY_TICKET
+#define GS_EARLY_TICKET 0
+#endif
 #ifndef GS_PREP_LATE_TRIGGER
 #define GS_PREP_LATE_TRIGGER 1
 #endif
@@ -358,7 +363,7 @@ __global__ void __launch_bounds__(kPrepThreads)
 k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32_t shift, FilterBuffers fb,
        const u64* __restrict__ used, const u64* __restrict__ cap, const uint32_t* __restrict__ nodeinfo,
        uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, uint32_t overlap_previous,
-       uint32_t expand_epoch_wanted) {
+       uint32_t expand_epoch_wanted, uint32_t blocks_wanted) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     __shared__ bool is_last;
     // Programmatic dependent launch, both ways.  This grid is launched as a programmatic dependent of whatever
@@ -472,7 +477,9 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
     GS_KTRACE(2 * (expand_epoch_wanted + 1) + fb.set_index, 0, 2);
     if (tid == 0) {
         __threadfence();
-        is_last = atomicAdd(fb.prep_done, 1u) == gridDim.x - 1;
+        // (a count of finished blocks over all launches on this buffer set, never reset: a CTA of k_expand that is let in
+        // after this point finds it at `blocks_wanted`)
+        is_last = atomicAdd(fb.prep_done, 1u) + 1u == blocks_wanted;
     }
     __syncthreads();
 #if GS_PREP_LATE_TRIGGER
@@ -485,9 +492,8 @@ k_prep(const u64* __restrict__ req, uint32_t n_pods, uint32_t pod_blocks, uint32
         reinterpret_cast<uint4*>(fb.pod_hist)[tid] = make_uint4(0, 0, 0, 0);
         __syncthreads();
         if (tid == 0) {
-            *fb.prep_done = 0;
             __threadfence();
-            atomicAdd(fb.prep_epoch, 1u);
+            atomicAdd(fb.prep_epoch, 1u);  // results complete AND bucket counts re-armed
             // A grid that did not wait at its start must still not complete before its predecessor does: later
             // work in the stream relies on completion being transitive.  One lingering thread is enough to hold
             // the grid open; every other block frees its SM resources at once.
@@ -618,7 +624,7 @@ template <bool kVec>
 __global__ void __launch_bounds__(kExpandThreads, kExpandThreads == 256 ? 5 : 8)
 k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_stride, uint32_t* __restrict__ out,
          uint32_t n_col_blocks, uint32_t inv_col_blocks, uint32_t n_tiles, uint32_t overlap_previous,
-         uint32_t prep_epoch_wanted) {
+         uint32_t prep_epoch_wanted, uint32_t prep_blocks_wanted) {
     __shared__ __align__(128) ExpandSmem sm;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr uint32_t kWarps = kExpandThreads / 32;
@@ -674,17 +680,17 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
 #if GS_PREP_LATE_TRIGGER
         // This grid is k_prep's programmatic dependent and k_prep's blocks trigger only after they have fenced what
         // they wrote: a CTA that runs here runs after all of them.  The first tile's inputs are therefore asked for at
-        // once, and the epoch -- read at the same time, not before -- only confirms it.  Should it ever not (a launch
+        // once, and the count of k_prep's finished blocks -- read at the same time, not before -- only confirms it.  Should it ever not (a launch
         // order this file does not produce), the CTA does what the other build does: waits for the epoch and asks
         // again; the count of such CTAs is readable through gs_debug_early_starts().
         if (tid == 0) {
             asm volatile("fence.proxy.async;" ::: "memory");
             request(blockIdx.x, 0);
-            uint32_t seen = ld_acquire_u32(fb.prep_epoch);
+            uint32_t seen = ld_acquire_u32(fb.prep_done);
 #ifdef GS_TEST_FORCE_EARLY_START
-            if ((blockIdx.x & 7u) == 3u) seen = prep_epoch_wanted - 1u;  // (test builds: exercise the path)
+            if ((blockIdx.x & 7u) == 3u) seen = prep_blocks_wanted - 1u;  // (test builds: exercise the path)
 #endif
-            if ((int32_t)(seen - prep_epoch_wanted) < 0) {
+            if ((int32_t)(seen - prep_blocks_wanted) < 0) {
                 atomicAdd(fb.early_starts, 1u);
                 if (blockIdx.x < n_tiles) mbar_wait(&tin_bar[0], 0, fb.fault, kFaultTileInputs);  // the copy asked for above
                 wait_epoch(fb.prep_epoch, prep_epoch_wanted, fb.fault, kFaultExpandEpoch);
@@ -718,6 +724,18 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         const uint32_t w0 = cb * kTileWords;
         const TileInputs& in = tin[stage];
         GS_TRACE(0);
+#if GS_EARLY_TICKET
+        // From a CTA's second tile on the ticket for the tile after this one is taken right here, so that its round trip
+        // is over when it is wanted (just before this tile's stores).  Dense tiles sit at the high buckets, which are
+        // the CTAs' FIRST tiles; only there is the ticket taken after the tile is known not to be dense.
+        bool have_ticket = false;  // thread 0
+        if (tid == 0 && it != 0) {
+            ticket = atomicAdd(&fb.sched[0], 1u);
+            have_ticket = true;
+        }
+#else
+        const bool have_ticket = false;
+#endif
         mbar_wait(&tin_bar[stage], parity, fb.fault, kFaultTileInputs);
         GS_TRACE(1);
 
@@ -789,7 +807,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             }
         }
 
-        if (!dense && tid == 0) ticket = atomicAdd(&fb.sched[0], 1u);  // consumed just before the stores
+        if (!dense && tid == 0 && !have_ticket) ticket = atomicAdd(&fb.sched[0], 1u);  // consumed just before the stores
 
         // Dense tiles want the tile's rows in ascending request order: then a node's column is a prefix of
         // ones and one binary search per node replaces a comparison per row.
@@ -959,7 +977,7 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
                     GS_TRACE(12);
                     // the ticket of a dense tile is taken late (see the schedule note above): when this warp's
                     // share of the last pass is done, so that the round trip overlaps the wait for the other warps
-                    if (tid == 0 && pass + 1 == passes) ticket = atomicAdd(&fb.sched[0], 1u);
+                    if (tid == 0 && pass + 1 == passes && !have_ticket) ticket = atomicAdd(&fb.sched[0], 1u);
                     __syncthreads();  // counts complete; the key area may be overwritten
                     GS_TRACE(13);
                 }
@@ -1101,6 +1119,9 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         if (atomicAdd(&fb.sched[1], 1u) == gridDim.x - 1) {
             fb.sched[0] = 0;
             fb.sched[1] = 0;
+            // (the next k_prep on this buffer set waits for the epoch below; by then this batch's k_prep must have
+            // re-armed its counters, which it does after letting this grid in)
+            if (overlap_previous) wait_epoch(fb.prep_epoch, prep_epoch_wanted, fb.fault, kFaultPrepEpoch);
             __threadfence();
             atomicAdd(fb.expand_epoch, 1u);
             // completion stays transitive along the stream even when this grid did not wait at its start
@@ -1146,7 +1167,7 @@ cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n
 cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do_nodes, uint32_t shift,
                         const FilterBuffers& fb, const u64* d_used, const u64* d_cap, const uint32_t* d_nodeinfo,
                         uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words, bool overlap_previous,
-                        uint32_t expand_epoch_wanted, cudaStream_t st) {
+                        uint32_t expand_epoch_wanted, uint32_t* blocks_total, cudaStream_t st) {
     const uint32_t pod_blocks = do_pods ? (n_pods + kPrepThreads - 1) / kPrepThreads : 0u;
     const uint32_t node_blocks = do_nodes ? (n_words + kPrepThreads / 32 - 1) / (kPrepThreads / 32) : 0u;
     if (pod_blocks + node_blocks == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
@@ -1161,16 +1182,21 @@ cudaError_t launch_prep(const u64* d_req, uint32_t n_pods, bool do_pods, bool do
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     const uint32_t ov = overlap_previous ? 1u : 0u;
+    const uint32_t blocks_wanted = *blocks_total + pod_blocks + node_blocks;  // what the set's block count reaches with this launch
+    cudaError_t e;
     if (dev_stride == 8)
-        return cudaLaunchKernelEx(&cfg, k_prep<8>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
-                                  dev_stride, n_words, ov, expand_epoch_wanted);
-    return cudaLaunchKernelEx(&cfg, k_prep<0>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
-                              dev_stride, n_words, ov, expand_epoch_wanted);
+        e = cudaLaunchKernelEx(&cfg, k_prep<8>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
+                               dev_stride, n_words, ov, expand_epoch_wanted, blocks_wanted);
+    else
+        e = cudaLaunchKernelEx(&cfg, k_prep<0>, d_req, n_pods, pod_blocks, shift, fb, d_used, d_cap, d_nodeinfo, n_nodes,
+                               dev_stride, n_words, ov, expand_epoch_wanted, blocks_wanted);
+    if (e == cudaSuccess) *blocks_total = blocks_wanted;
+    return e;
 }
 
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
                           uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted,
-                          cudaStream_t st) {
+                          uint32_t prep_blocks_wanted, cudaStream_t st) {
     if (n_pods == 0 || words == 0) return cudaErrorInvalidValue;  // callers count launches: never a silent no-op
     {
         int dev = 0;
@@ -1214,9 +1240,9 @@ cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods
     cfg.numAttrs = 1;
     if (vec)
         return cudaLaunchKernelEx(&cfg, k_expand<true>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles, ov,
-                                  prep_epoch_wanted);
+                                  prep_epoch_wanted, prep_blocks_wanted);
     return cudaLaunchKernelEx(&cfg, k_expand<false>, fb, n_pods, words_out, row_stride, d_out, n_col_blocks, inv, n_tiles, ov,
-                              prep_epoch_wanted);
+                              prep_epoch_wanted, prep_blocks_wanted);
 }
 
 }  // namespace gs

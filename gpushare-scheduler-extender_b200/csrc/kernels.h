@@ -20,7 +20,7 @@ struct FilterBuffers {              // work buffers of one filter launch sequenc
     unsigned long long* node_key;     // [words * 32] max available memory per node
     uint32_t* node_key32;             // [words * 32] the same, saturated to 32 bits
     uint32_t* sched;                  // [2] tile scheduler of k_expand (self re-arming)
-    uint32_t* prep_done;              // [1] finished blocks of the running k_prep (self re-arming)
+    uint32_t* prep_done;              // [1] finished k_prep blocks of all launches on this buffer set (never reset)
     uint32_t* prep_epoch;             // [1] completed k_prep launches on this buffer set
     uint32_t* expand_epoch;           // [1] completed k_expand launches on this buffer set
     uint32_t set_index;               // 0 / 1: which of the two buffer sets this is (development traces)
@@ -32,10 +32,11 @@ cudaError_t launch_sort_binds(int device, const gs_bind_req* d_binds, uint32_t n
 cudaError_t launch_prep(const unsigned long long* d_req, uint32_t n_pods, bool do_pods, bool do_nodes, uint32_t shift,
                         const FilterBuffers& fb, const unsigned long long* d_used, const unsigned long long* d_cap,
                         const uint32_t* d_nodeinfo, uint32_t n_nodes, uint32_t dev_stride, uint32_t n_words,
-                        bool overlap_previous, uint32_t expand_epoch_wanted, cudaStream_t st);
+                        bool overlap_previous, uint32_t expand_epoch_wanted, uint32_t* blocks_total,
+                        cudaStream_t st);
 cudaError_t launch_expand(int sm_count, const FilterBuffers& fb, uint32_t n_pods, uint32_t words,
                           uint32_t row_stride, uint32_t* d_out, bool overlap_previous, uint32_t prep_epoch_wanted,
-                          cudaStream_t st);
+                          uint32_t prep_blocks_wanted, cudaStream_t st);
 
 // K1 / K2 / K4 (state_kernels.cu)
 cudaError_t launch_validate_records(gs_pod_record* d_pods, uint32_t first, uint32_t n, const uint32_t* d_nodeinfo,
