@@ -686,7 +686,8 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
         if (tid == 0) {
             asm volatile("fence.proxy.async;" ::: "memory");
             request(blockIdx.x, 0);
-            uint32_t seen = ld_acquire_u32(fb.prep_done);
+            uint32_t seen;  // (relaxed: it confirms, it does not order; the path that waits uses an acquiring read)
+            asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(fb.prep_done) : "memory");
 #ifdef GS_TEST_FORCE_EARLY_START
             if ((blockIdx.x & 7u) == 3u) seen = prep_blocks_wanted - 1u;  // (test builds: exercise the path)
 #endif
