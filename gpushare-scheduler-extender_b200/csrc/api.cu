@@ -416,9 +416,9 @@ uint32_t expand_words_out(uint32_t words, uint32_t row_stride, const void* d_out
     return w;
 }
 
-// host_side: d_req, d_rank and d_cutoff are the device's view of page-locked host memory
+// host_req / host_cut: d_req / d_cutoff are the device's view of page-locked host memory
 int compact_device_locked(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32_t n_pods, uint16_t* d_rank,
-                          uint32_t rank_stride, uint16_t* d_cutoff, cudaStream_t st, bool host_side = false) {
+                          uint32_t rank_stride, uint16_t* d_cutoff, cudaStream_t st, bool host_req = false, bool host_cut = false) {
     if (rank_stride < s->n_nodes) return fail(GS_ERR_INVALID, "rank_stride %u < node count %u", rank_stride, s->n_nodes);
     c.prev_filter = false;  // (a snapshot without nodes still answers: the cutoffs depend on the requests only)
     for (uint32_t p0 = 0, k = 0; p0 < n_pods; p0 += GS_MAX_BATCH, ++k) {
@@ -433,7 +433,7 @@ int compact_device_locked(gs_snapshot* s, FilterCtx& c, const u64* d_req, uint32
             dsts.count = s->n_nodes;
             le = gs::launch_compact(d_req + p0, n, c.d_cslices, c.d_csorted, c.d_cdup, s->d_used, s->d_cap, s->d_nodeinfo,
                                     s->n_nodes, s->max_devs, dsts, d_cutoff + p0, s->sm_count, st, &launched,
-                                    host_side ? c.d_creq : nullptr, host_side ? c.d_ccut : nullptr);
+                                    host_req ? c.d_creq : nullptr, host_cut ? c.d_ccut : nullptr);
             return le;
         });
         s->launches += launched;
@@ -887,9 +887,8 @@ int gs_filter_batch_compact_device(gs_snapshot* s, const uint64_t* d_req, uint32
     if (rc) return rc;
     l.c->outstanding = true;
     // (buffers from gs_host_alloc are "device" buffers too: the kernels then touch host memory as little as they can)
-    const bool host_side = in_host_block(d_req) && in_host_block(d_out_cutoff);
     return compact_device_locked(s, *l.c, reinterpret_cast<const u64*>(d_req), n_pods, d_out_rank, rank_stride, d_out_cutoff, st,
-                                 host_side);
+                                 in_host_block(d_req), in_host_block(d_out_cutoff));
 }
 
 int gs_filter_batch_compact_device_gather(gs_snapshot* s, const uint64_t* d_req, uint32_t n_pods, uint16_t* const* d_rank_dsts,
@@ -948,7 +947,7 @@ int gs_filter_batch_compact(gs_snapshot* s, const uint64_t* req, uint32_t n_pods
             rc = order_filter(s, c, c.stream);
             if (rc) return rc;
             c.outstanding = true;
-            rc = compact_device_locked(s, c, v_req, n_pods, v_rank, rank_stride, v_cut, c.stream, true);
+            rc = compact_device_locked(s, c, v_req, n_pods, v_rank, rank_stride, v_cut, c.stream, true, true);
             if (rc) return rc;
             CU(cudaStreamSynchronize(c.stream));
             return GS_OK;
