@@ -293,6 +293,12 @@ __device__ __forceinline__ void wait_epoch(const uint32_t* p, uint32_t want, uns
 // step instead of 13.9).
 // (1: from a CTA's second tile on the ticket is taken at the top of the tile -- measured slower: 14.2 vs 14.0 us per step,
 // 16.4 vs 15.5 us alone; profiles/NOTES.md 34)
+#ifndef GS_EXPAND_W0_LIGHT
+#define GS_EXPAND_W0_LIGHT 1
+#endif
+#ifndef GS_EXPAND_W0_ROWS
+#define GS_EXPAND_W0_ROWS 0
+#endif
 #ifndef GS_EARLY_TICKET
 #define GS_EARLY_TICKET 0
 #endif
@@ -860,9 +866,29 @@ k_expand(FilterBuffers fb, uint32_t n_pods, uint32_t words_out, uint32_t row_str
             p4 = *reinterpret_cast<const uint32_t*>(&sm.pidx[lcol * 4]);
             if (wcol < words_out && p4 == 0xffffffffu) {
                 uint32_t* dst = out + wcol;
+#if GS_EXPAND_W0_LIGHT
+                // Warp 0 is the one that waits for the ticket and issues the next tile's input copies before it stores,
+                // and the tile ends when its last warp has stored: in a full-width tile warp 0 keeps only the first
+                // kW0Rows of its eight rows (0, 8, 16, ...), the others go round warps 1..7, one row each.
+                constexpr uint32_t kW0Rows = GS_EXPAND_W0_ROWS;
+                const bool light = lane_shift == 5u;
+                const uint32_t my_end = (light && warp == 0) ? min(rows, kW0Rows * kWarps) : rows;
+#pragma unroll 4
+                for (uint32_t rr = row0; rr < my_end; rr += row_step)
+                    __stcs(reinterpret_cast<uint4*>(dst + sm.row_off[rr]), b4);
+                if (light && warp != 0) {
+#pragma unroll
+                    for (uint32_t i = kW0Rows; i < kTileRows / kWarps; ++i) {
+                        const uint32_t rr = i * kWarps;  // a row of warp 0
+                        if ((i - kW0Rows) % (kWarps - 1) + 1 == warp && rr < rows)
+                            __stcs(reinterpret_cast<uint4*>(dst + sm.row_off[rr]), b4);
+                    }
+                }
+#else
 #pragma unroll 4
                 for (uint32_t rr = row0; rr < rows; rr += row_step)
                     __stcs(reinterpret_cast<uint4*>(dst + sm.row_off[rr]), b4);
+#endif
             }
         } else {
             for (uint32_t rr = warp; rr < rows; rr += kWarps) {
