@@ -111,6 +111,66 @@ def test_filters_beside_event_batches_see_a_prefix_of_the_writes():
         assert K in seen
 
 
+def test_in_place_filters_beside_single_binds_see_a_prefix_of_the_binds():
+    """The request-at-a-time routes under concurrency: one thread binds pods one by one (the one-warp kernel, in place in
+    the page-locked block), three threads filter all the while -- the compact form into their own page-locked buffers
+    (kernels writing host memory in place) and a small candidate list (in place in the context's block).  Every answer
+    must be the answer for the state after some whole number of binds, and time must not run backwards."""
+    sc = synth.make_cluster(64, 4, 16384, running=0, seed=5, quirks=False)
+    cap, ndev, cls = sc.dev_capacity(), sc.dev_count(), sc.node_class()
+    reqs = np.array([1, 5000, 9000, 16384], np.uint64)
+    K = 120
+    rng = np.random.default_rng(5)
+    binds = synth.bind_records(rng.integers(0, 8, K), rng.choice([4096, 8192], K), first_slot=0)   # eight hot nodes
+    used = np.zeros((sc.n_nodes, 4), np.uint64)
+    table = np.zeros(K, synth.POD_DT)
+    states = []
+    key, elig = S.node_keys(cap, used, ndev, cls)
+    states.append(S.filter_pass(reqs, key, elig))
+    want_dev = []
+    for k in range(K):
+        want_dev.append(int(S.bind_sequential(binds[k:k + 1], cap, used, ndev, cls, table)[0]))
+        key, elig = S.node_keys(cap, used, ndev, cls)
+        states.append(S.filter_pass(reqs, key, elig))
+    sub = np.arange(16, dtype=np.uint32)
+    with gsx.Snapshot(sc.n_nodes, 4, K) as s:
+        s.node_upsert(sc.gs_nodes())
+        done = threading.Event()
+
+        def writer():
+            for k in range(K):
+                assert int(s.bind_batch(binds[k:k + 1])[0]) == want_dev[k], k
+            done.set()
+
+        def reader(kind):
+            def run():
+                h_req = gsx.PinnedBuffer(len(reqs), np.uint64)
+                h_rank = gsx.PinnedBuffer((1, sc.n_nodes), np.uint16)
+                h_cut = gsx.PinnedBuffer(len(reqs), np.uint16)
+                h_req.array[:] = reqs
+                last = 0
+                while True:
+                    finished = done.is_set()
+                    if kind == "compact":
+                        rank, cut = s.filter_batch_compact(h_req.array, out_rank=h_rank.array, out_cutoff=h_cut.array)
+                        bits = rank[0][None, :] >= cut[:, None]
+                        match = [j for j in range(last, K + 1) if (bits == states[j]).all()]
+                    else:
+                        bits = gsx.unpack_bitmap(s.filter_batch_subset(reqs, sub), len(sub))
+                        match = [j for j in range(last, K + 1) if (bits == states[j][:, :16]).all()]
+                    assert match, "a filter saw a state that is no prefix of the binds"
+                    last = match[0]
+                    if finished:
+                        assert (bits == (states[K] if kind == "compact" else states[K][:, :16])).all()
+                        for b in (h_req, h_rank, h_cut):
+                            b.free()
+                        return
+            return run
+
+        _run_threads([writer, reader("compact"), reader("subset"), reader("compact")])
+        assert (s.read_used() == used).all()
+
+
 def test_two_snapshots_pipeline_on_one_gpu_from_two_threads():
     """Two snapshots, each driven from its own host thread on its own stream with overlapping filters switched
     on, share cuda:0: their kernels interleave on the SMs, and each keeps to its own work buffers and counters."""
