@@ -83,3 +83,29 @@ if rows:
     print(f"{len(t)} sparse tiles, partial words median {int(np.median(t[:, 8] & 0xffff))}: " +
           ", ".join(f"{n} {int(np.median(t[:, b] - t[:, a]))}" for n, (a, b) in zip(sn, ss)) +
           f"; whole {int(np.median(t[:, 7] - t[:, 0]))} cycles (max {int((t[:, 7] - t[:, 0]).max())})")
+
+# per-CTA view of the LAST launch: when each CTA classified its tiles (globaltimer, stamp 9), of what kind they were
+gt = tr[:, :, 9]
+kind = np.where(((tr[:, :, 8] >> 16) & 1) == 1, 2, np.where((tr[:, :, 8] & 0xffff) != 0, 1, 0))   # 0 clean, 1 sparse, 2 dense
+valid = (tr[:, :, 7] > tr[:, :, 0]) & (tr[:, :, 0] > 0) & (gt > 0)
+n_t = valid.sum(axis=1)
+act = n_t > 0
+if act.any():
+    t0l = gt[valid].min()
+    last_start = np.array([gt[c, :][valid[c]].max() if n_t[c] else 0 for c in range(gt.shape[0])])
+    cyc_last = np.array([int(tr[c, n_t[c] - 1, 7] - tr[c, n_t[c] - 1, 0]) if 0 < n_t[c] <= kT else 0 for c in range(gt.shape[0])])
+    end_est = (last_start - t0l) / 1e3 + cyc_last / 1965.0     # us after the first classification of the launch
+    print(f"last launch: {int(act.sum())} CTAs; tiles per CTA (<= {kT} recorded): " + ", ".join(f"{k}: {int((n_t[act] == k).sum())}" for k in range(1, kT + 1)))
+    print("end of a CTA's last recorded tile, us after the launch's first classification: min %.1f median %.1f p90 %.1f max %.1f" %
+          (end_est[act].min(), np.median(end_est[act]), np.percentile(end_est[act], 90), end_est[act].max()))
+    order_c = np.argsort(-end_est)
+    for c in order_c[:8]:
+        if not act[c]:
+            continue
+        ks = "".join("CSD"[kind[c, i]] for i in range(n_t[c]))
+        st = ", ".join(f"{(gt[c, i] - t0l) / 1e3:.1f}" for i in range(n_t[c]))
+        print(f"  CTA {c}: tiles {ks}, classified at {st} us, ends ~{end_est[c]:.1f} us")
+    for k in (0, 1, 2):
+        first = kind[:, 0] == k
+        if (first & act).any():
+            print(f"  CTAs whose first tile is {'clean sparse dense'.split()[k]}: {int((first & act).sum())}, end median {np.median(end_est[first & act]):.1f} max {end_est[first & act].max():.1f} us")
